@@ -1,0 +1,250 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU oracles for the eikonal trace/backtrace path.
+
+Three checkers, all taking and returning host numpy arrays (ray vectors AoS
+``(N,3)``, grids flat or 3-D C-contiguous, index ``(z*H+y)*W+x`` with
+``(W,H,D) = res`` as in ``/root/reference/src/volume.cpp:134``):
+
+``port``    the plain-C float32 restatement ``oracle/eikonal_oracle.c``
+``port64``  the same source built with ``real = double`` (arbitration only)
+``ref``     the reference's own ``Tracer<false,false>`` compiled from
+            ``/root/reference`` by ``oracle/build_ref.sh`` (``oracle/_ref/``);
+            ``None`` if that library has not been built.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline /
+``--impl reference`` legs may import this package.  The product package
+``adjointnonlinearraytracing_b200`` never does.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+from ctypes import POINTER, c_float, c_double, c_int, c_int64, c_uint8, c_char_p
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_i64 = c_int64
+
+
+def build(verbose: bool = False) -> None:
+    """Compile the C restatement (and the reference library when its sources exist)."""
+    out = subprocess.run(["make", "-C", _HERE], capture_output=True, text=True)
+    if out.returncode != 0:
+        raise RuntimeError("oracle build failed:\n" + out.stdout + out.stderr)
+    if verbose:
+        print(out.stdout)
+
+
+def _cpu_has_avx512() -> bool:
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("flags"):
+                    fl = set(line.split(":", 1)[1].split())
+                    return {"avx512f", "avx512vl", "avx512dq", "avx512bw", "avx512cd"} <= fl
+    except OSError:
+        pass
+    return False
+
+
+def _f32(a, shape=None):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    return a if shape is None else a.reshape(shape)
+
+
+class _Lib:
+    """ctypes wrapper shared by the three checkers (same call shapes)."""
+
+    def __init__(self, path: str, prefix: str, real=np.float32, returns_steps: bool = True):
+        self.path = path
+        self.lib = ctypes.CDLL(path)
+        self.prefix = prefix
+        self.real = np.dtype(real)
+        self.creal = c_float if self.real == np.float32 else c_double
+        self.returns_steps = returns_steps
+        self.last_steps = None
+
+    # -- helpers ---------------------------------------------------------
+    def _fn(self, name, restype=None):
+        f = getattr(self.lib, self.prefix + name)
+        f.restype = restype if restype is not None else (_i64 if self.returns_steps else c_int)
+        return f
+
+    def _a(self, x):
+        return np.ascontiguousarray(x, dtype=self.real)
+
+    def _p(self, a):
+        return a.ctypes.data_as(POINTER(self.creal))
+
+    def _check(self, rc):
+        if self.returns_steps:
+            self.last_steps = int(rc)
+        elif rc != 0:
+            f = self.lib.ref_last_error
+            f.restype = c_char_p
+            raise RuntimeError(f().decode())
+
+    @staticmethod
+    def _res(rif, res):
+        if res is None:
+            res = tuple(rif.shape)
+        W, H, D = (int(r) for r in res)
+        if W * H * D != rif.size:
+            raise RuntimeError("Resolution doesn't match data")
+        return W, H, D
+
+    # -- forward ---------------------------------------------------------
+    def trace(self, rif, pos, vel, h, ds, res=None):
+        rif = self._a(rif); W, H, D = self._res(rif, res)
+        pos = self._a(pos); vel = self._a(vel); N = pos.shape[0]
+        xt = np.empty_like(pos); vt = np.empty_like(pos)
+        rc = self._fn("trace")(self._p(rif), W, H, D, self._p(pos), self._p(vel), _i64(N),
+                               self.creal(h), self.creal(ds), self._p(xt), self._p(vt))
+        self._check(rc)
+        return xt, vt
+
+    def trace_pln(self, rif, pos, vel, pln_o, pln_d, h, ds, res=None):
+        rif = self._a(rif); W, H, D = self._res(rif, res)
+        pos = self._a(pos); vel = self._a(vel); po = self._a(pln_o); pd = self._a(pln_d)
+        N = pos.shape[0]
+        xt = np.empty_like(pos); vt = np.empty_like(pos); m = np.zeros(N, dtype=np.uint8)
+        rc = self._fn("trace_plane")(self._p(rif), W, H, D, self._p(pos), self._p(vel), self._p(po),
+                                     self._p(pd), _i64(N), self.creal(h), self.creal(ds),
+                                     self._p(xt), self._p(vt), m.ctypes.data_as(POINTER(c_uint8)))
+        self._check(rc)
+        return xt, vt, m.astype(bool)
+
+    def trace_target(self, rif, pos, vel, target, h, ds, res=None):
+        rif = self._a(rif); W, H, D = self._res(rif, res)
+        pos = self._a(pos); vel = self._a(vel); t = self._a(target); N = pos.shape[0]
+        xt = np.empty_like(pos); vt = np.empty_like(pos); d2 = np.empty(N, dtype=self.real)
+        rc = self._fn("trace_target")(self._p(rif), W, H, D, self._p(pos), self._p(vel), self._p(t),
+                                      _i64(N), self.creal(h), self.creal(ds), self._p(xt),
+                                      self._p(vt), self._p(d2))
+        self._check(rc)
+        return xt, vt, d2
+
+    def trace_sdf(self, rif, sdf, pos, vel, h, ds, res=None):
+        rif = self._a(rif); sdf = self._a(sdf); W, H, D = self._res(rif, res)
+        pos = self._a(pos); vel = self._a(vel); N = pos.shape[0]
+        xt = np.empty_like(pos); vt = np.empty_like(pos)
+        rc = self._fn("trace_sdf")(self._p(rif), self._p(sdf), W, H, D, self._p(pos), self._p(vel),
+                                   _i64(N), self.creal(h), self.creal(ds), self._p(xt), self._p(vt))
+        self._check(rc)
+        return xt, vt
+
+    def trace_cable(self, rif, radius, length, pos, vel, target, ds):
+        rif = self._a(rif).ravel(); pos = self._a(pos); vel = self._a(vel); t = self._a(target)
+        N = pos.shape[0]
+        xt = np.empty_like(pos); vt = np.empty_like(pos); d2 = np.empty(N, dtype=self.real)
+        rc = self._fn("trace_cable")(self._p(rif), c_int(rif.size), self.creal(radius),
+                                     self.creal(length), self._p(pos), self._p(vel), self._p(t),
+                                     _i64(N), self.creal(ds), self._p(xt), self._p(vt), self._p(d2))
+        self._check(rc)
+        return xt, vt, d2
+
+    # -- adjoint ---------------------------------------------------------
+    def backtrace(self, rif, xt, vt, dx, dv, h, ds, res=None):
+        rif = self._a(rif); W, H, D = self._res(rif, res)
+        xt = self._a(xt); vt = self._a(vt); dx = self._a(dx); dv = self._a(dv); N = xt.shape[0]
+        g = np.empty(rif.size, dtype=self.real)
+        rc = self._fn("backtrace")(self._p(rif), W, H, D, self._p(xt), self._p(vt), self._p(dx),
+                                   self._p(dv), _i64(N), self.creal(h), self.creal(ds), self._p(g))
+        self._check(rc)
+        return g.reshape(rif.shape)
+
+    def backtrace_sdf(self, rif, sdf, xt, vt, dx, dv, h, ds, res=None):
+        rif = self._a(rif); sdf = self._a(sdf); W, H, D = self._res(rif, res)
+        xt = self._a(xt); vt = self._a(vt); dx = self._a(dx); dv = self._a(dv); N = xt.shape[0]
+        g = np.empty(rif.size, dtype=self.real)
+        rc = self._fn("backtrace_sdf")(self._p(rif), self._p(sdf), W, H, D, self._p(xt),
+                                       self._p(vt), self._p(dx), self._p(dv), _i64(N),
+                                       self.creal(h), self.creal(ds), self._p(g))
+        self._check(rc)
+        return g.reshape(rif.shape)
+
+    def backtrace_cable(self, rif, radius, length, xt, vt, dx, dv, ds):
+        rif = self._a(rif).ravel()
+        xt = self._a(xt); vt = self._a(vt); dx = self._a(dx); dv = self._a(dv); N = xt.shape[0]
+        g = np.empty(rif.size, dtype=self.real)
+        rc = self._fn("backtrace_cable")(self._p(rif), c_int(rif.size), self.creal(radius),
+                                         self.creal(length), self._p(xt), self._p(vt), self._p(dx),
+                                         self._p(dv), _i64(N), self.creal(ds), self._p(g))
+        self._check(rc)
+        return g
+
+    # -- volume probes ---------------------------------------------------
+    def volume_eval(self, rif, pos, h, res=None):
+        rif = self._a(rif); W, H, D = self._res(rif, res); pos = self._a(pos); N = pos.shape[0]
+        n = np.empty(N, dtype=self.real); g = np.empty((N, 3), dtype=self.real)
+        hs = np.empty((N, 3), dtype=self.real)
+        rc = self._fn("volume_eval", None if not self.returns_steps else c_int)(
+            self._p(rif), W, H, D, self._p(pos), _i64(N), self.creal(h), self._p(n), self._p(g),
+            self._p(hs))
+        if not self.returns_steps:
+            self._check(rc)
+        return n, g, hs
+
+    def volume_splat(self, data, pos, val, grad, h, res=None):
+        data = self._a(data).copy(); W, H, D = self._res(data, res)
+        pos = self._a(pos); val = self._a(val); grad = self._a(grad); N = pos.shape[0]
+        rc = self._fn("volume_splat", None if not self.returns_steps else c_int)(
+            self._p(data), W, H, D, self._p(pos), self._p(val), self._p(grad), _i64(N),
+            self.creal(h))
+        if not self.returns_steps:
+            self._check(rc)
+        return data
+
+    def cylinder_eval(self, rif, radius, length, pos):
+        rif = self._a(rif).ravel(); pos = self._a(pos); N = pos.shape[0]
+        n = np.empty(N, dtype=self.real); g = np.empty((N, 3), dtype=self.real)
+        hs = np.empty((N, 3, 3), dtype=self.real)
+        rc = self._fn("cylinder_eval", None if not self.returns_steps else c_int)(
+            self._p(rif), c_int(rif.size), self.creal(radius), self.creal(length), self._p(pos),
+            _i64(N), self._p(n), self._p(g), self._p(hs))
+        if not self.returns_steps:
+            self._check(rc)
+        return n, g, hs
+
+    def cylinder_splat(self, data, radius, length, pos, val, grad):
+        data = self._a(data).ravel().copy(); pos = self._a(pos); val = self._a(val)
+        grad = self._a(grad); N = pos.shape[0]
+        rc = self._fn("cylinder_splat", None if not self.returns_steps else c_int)(
+            self._p(data), c_int(data.size), self.creal(radius), self.creal(length), self._p(pos),
+            self._p(val), self._p(grad), _i64(N))
+        if not self.returns_steps:
+            self._check(rc)
+        return data
+
+
+def _load_port(name, prefix, real):
+    path = os.path.join(_HERE, "_build", name)
+    if not os.path.exists(path):
+        build()
+    return _Lib(path, prefix, real, returns_steps=True)
+
+
+def _load_ref():
+    cands = ["libdrrt_ref_v4.so", "libdrrt_ref_v3.so"] if _cpu_has_avx512() else ["libdrrt_ref_v3.so"]
+    for c in cands:
+        path = os.path.join(_HERE, "_ref", c)
+        if os.path.exists(path):
+            return _Lib(path, "ref_", np.float32, returns_steps=False)
+    return None
+
+
+_cache = {}
+
+
+def __getattr__(name):
+    if name in ("port", "port64", "ref"):
+        if name not in _cache:
+            if name == "port":
+                _cache[name] = _load_port("liborc.so", "orc_", np.float32)
+            elif name == "port64":
+                _cache[name] = _load_port("liborc64.so", "orc64_", np.float64)
+            else:
+                _cache[name] = _load_ref()
+        return _cache[name]
+    raise AttributeError(name)
