@@ -1,0 +1,326 @@
+// C ABI of libdrrt_b200.so (see include/drrt_b200.h for the contract and the
+// reference interface each entry point replaces).
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <dlfcn.h>
+#include <string>
+
+#include "../../include/drrt_b200.h"
+#include "drrt_launch.h"
+
+using namespace drrt;
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<int64_t> g_launches{0};
+
+int fail(int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CU_TRY(expr)                                                              \
+  do {                                                                            \
+    cudaError_t e_ = (expr);                                                      \
+    if (e_ != cudaSuccess) return fail(DRRT_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e_)); \
+  } while (0)
+
+int check_launch(const char *what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(DRRT_ERR_CUDA, "%s launch failed: %s", what, cudaGetErrorString(e));
+  return DRRT_OK;
+}
+
+// Loop caps are evaluated in float and truncated, reference src/tracer.cpp:51,
+// :262, :417 (`int max_steps = 4 * h * hmax(res) / delta_s`).
+int cap_grid(float mult, float h, int W, int H, int D, float ds) {
+  int m = W > H ? W : H;
+  if (D > m) m = D;
+  float f = mult * h * (float) m / ds;
+  if (!(f > 0.f)) return 0;
+  if (f > 2.0e9f) return 2000000000;
+  return (int) f;
+}
+
+int cap_cable(float length, float ds) {  // src/tracer.cpp:332, :544
+  float f = 4 * length / ds;
+  if (!(f > 0.f)) return 0;
+  if (f > 2.0e9f) return 2000000000;
+  return (int) f;
+}
+
+int make_grid(GridP &g, const float *rif, int W, int H, int D, float h) {
+  if (W <= 0 || H <= 0 || D <= 0 || (int64_t) W * H * D > (int64_t) INT_MAX)
+    return fail(DRRT_ERR_RESOLUTION, "Resolution doesn't match data");
+  // volume::eval_grad, reference src/volume.cpp:117-124
+  if (!(W == 1 && H == 1 && D == 1) && (W < 2 || H < 2))
+    return fail(DRRT_ERR_RESOLUTION, "volume: invalid resolution!");
+  if (!rif) return fail(DRRT_ERR_INVALID_ARGUMENT, "rif is NULL");
+  if (!(h > 0.f)) return fail(DRRT_ERR_INVALID_ARGUMENT, "h must be positive");
+  g.data = rif;
+  g.W = W; g.H = H; g.D = D;
+  g.h = h;
+  g.rcp_h = 1.0f / h;
+  g.hix = (float) (W - 1) * h;
+  g.hiy = (float) (H - 1) * h;
+  g.hiz = (float) (D - 1) * h;
+  return DRRT_OK;
+}
+
+int make_cable(CableP &c, const float *rif, int res, float radius, float length) {
+  if (res < 2) return fail(DRRT_ERR_RESOLUTION, "cable profile needs at least 2 samples");
+  if (!rif) return fail(DRRT_ERR_INVALID_ARGUMENT, "rif is NULL");
+  c.data = rif;
+  c.res = res;
+  c.radius = radius;
+  c.length = length;
+  c.h = radius / (float) (res - 1);
+  c.r2 = radius * radius;
+  return DRRT_OK;
+}
+
+int check_rays(int64_t N, int layout, float ds) {
+  if (N < 0) return fail(DRRT_ERR_INVALID_ARGUMENT, "negative ray count");
+  if (layout != DRRT_SOA && layout != DRRT_AOS)
+    return fail(DRRT_ERR_INVALID_ARGUMENT, "layout must be DRRT_SOA (1) or DRRT_AOS (3)");
+  if (!(ds > 0.f)) return fail(DRRT_ERR_INVALID_ARGUMENT, "ds must be positive");
+  return DRRT_OK;
+}
+
+constexpr size_t kFixedTail = 16;  // max_bits word, padded
+
+int trace_common(int kind, const float *rif, const float *sdf, int W, int H, int D,
+                 const float *pos, const float *vel, const float *aux0, const float *aux1,
+                 int64_t N, int layout, float h, float ds, float *xt, float *vt,
+                 uint8_t *not_escaped, float *dist2, int64_t *stats, unsigned flags,
+                 cudaStream_t s) {
+  TraceArgs a;
+  memset(&a, 0, sizeof a);
+  int rc = make_grid(a.grid, rif, W, H, D, h);
+  if (rc) return rc;
+  if ((rc = check_rays(N, layout, ds))) return rc;
+  if (N == 0) return DRRT_OK;
+  if (!pos || !vel || !xt || !vt) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL ray buffer");
+  a.sdf = sdf; a.pos = pos; a.vel = vel; a.aux0 = aux0; a.aux1 = aux1;
+  a.N = N; a.layout = layout; a.ds = ds;
+  a.max_steps = cap_grid(kind == 3 ? 2.0f : 4.0f, h, W, H, D, ds);
+  a.xt = xt; a.vt = vt; a.not_escaped = not_escaped; a.dist2 = dist2; a.stats = stats;
+  void *tail = nullptr;
+  if (kind == 2) {
+    // SoA scratch for the batch-coupled tail: x, v (3N floats each), iters (N), max (1)
+    size_t bytes = sizeof(float) * 6 * (size_t) N + sizeof(int) * ((size_t) N + 4);
+    CU_TRY(cudaMallocAsync(&tail, bytes, s));
+    a.tail_x = (float *) tail;
+    a.tail_v = a.tail_x + 3 * N;
+    a.tail_iters = (int *) (a.tail_v + 3 * N);
+    a.tail_max_iters = a.tail_iters + N;
+    CU_TRY(cudaMemsetAsync(a.tail_max_iters, 0, sizeof(int), s));
+  }
+  g_launches += launch_trace(kind, (flags & DRRT_REFERENCE_ARITH) != 0, a, s);
+  rc = check_launch("trace");
+  if (tail) cudaFreeAsync(tail, s);
+  return rc;
+}
+
+int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, int H, int D,
+                     const float *xt, const float *vt, const float *dx, const float *dv, int64_t N,
+                     int layout, float h, float ds, float *grad, void *scratch, int64_t *stats,
+                     unsigned flags, cudaStream_t s) {
+  AdjArgs a;
+  memset(&a, 0, sizeof a);
+  int rc = make_grid(a.grid, rif, W, H, D, h);
+  if (rc) return rc;
+  if ((rc = check_rays(N, layout, ds))) return rc;
+  if (!grad) return fail(DRRT_ERR_INVALID_ARGUMENT, "grad is NULL");
+  const int64_t G = (int64_t) W * H * D;
+  const bool det = (flags & DRRT_DETERMINISTIC) != 0;
+  const bool accumulate = (flags & DRRT_ACCUMULATE) != 0;
+  if (det && !scratch) return fail(DRRT_ERR_INVALID_ARGUMENT, "DRRT_DETERMINISTIC needs a scratch buffer");
+  if (!accumulate) CU_TRY(cudaMemsetAsync(grad, 0, sizeof(float) * (size_t) G, s));  // src/tracer.cpp:401
+  if (N == 0) return DRRT_OK;
+  if (!xt || !vt || !dx || !dv) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL ray buffer");
+  a.sdf = sdf; a.xt = xt; a.vt = vt; a.dx = dx; a.dv = dv;
+  a.N = N; a.layout = layout; a.ds = ds; a.stats = stats;
+  a.max_steps = cap_grid(2.0f, h, W, H, D, ds);
+  unsigned long long *fixed = nullptr;
+  unsigned *max_bits = nullptr;
+  if (det) {
+    fixed = (unsigned long long *) scratch;
+    max_bits = (unsigned *) ((char *) scratch + sizeof(unsigned long long) * (size_t) G);
+    CU_TRY(cudaMemsetAsync(scratch, 0, sizeof(unsigned long long) * (size_t) G + kFixedTail, s));
+    g_launches += launch_fixed_max(dx, dv, 3 * N, max_bits, s);
+  }
+  g_launches += launch_backtrace(sdf_kind, (flags & DRRT_REFERENCE_ARITH) != 0, a, grad, fixed, max_bits, s);
+  if (det) g_launches += launch_fixed_to_float(fixed, max_bits, grad, G, accumulate, s);
+  return check_launch("backtrace");
+}
+
+}  // namespace
+
+extern "C" {
+
+int drrt_abi_version(void) { return DRRT_ABI_VERSION; }
+const char *drrt_last_error(void) { return g_err.c_str(); }
+// internal: lets drrt_host.cu report through the same per-thread slot
+void drrt_set_error_(const char *msg) { g_err = msg ? msg : ""; }
+int64_t drrt_launch_count(void) { return g_launches.load(); }
+
+int drrt_trace(const float *rif, int W, int H, int D, const float *pos, const float *vel,
+               int64_t N, int layout, float h, float ds, float *xt, float *vt, int64_t *stats,
+               unsigned flags, drrt_stream_t stream) {
+  return trace_common(0, rif, nullptr, W, H, D, pos, vel, nullptr, nullptr, N, layout, h, ds, xt, vt,
+                      nullptr, nullptr, stats, flags, (cudaStream_t) stream);
+}
+
+int drrt_trace_plane(const float *rif, int W, int H, int D, const float *pos, const float *vel,
+                     const float *pln_o, const float *pln_d, int64_t N, int layout, float h,
+                     float ds, float *xt, float *vt, uint8_t *not_escaped, int64_t *stats,
+                     unsigned flags, drrt_stream_t stream) {
+  if (N > 0 && (!pln_o || !pln_d || !not_escaped)) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL plane buffer");
+  return trace_common(1, rif, nullptr, W, H, D, pos, vel, pln_o, pln_d, N, layout, h, ds, xt, vt,
+                      not_escaped, nullptr, stats, flags, (cudaStream_t) stream);
+}
+
+int drrt_trace_target(const float *rif, int W, int H, int D, const float *pos, const float *vel,
+                      const float *target, int64_t N, int layout, float h, float ds, float *xt,
+                      float *vt, float *dist2, int64_t *stats, unsigned flags,
+                      drrt_stream_t stream) {
+  if (N > 0 && (!target || !dist2)) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL target buffer");
+  return trace_common(2, rif, nullptr, W, H, D, pos, vel, target, nullptr, N, layout, h, ds, xt, vt,
+                      nullptr, dist2, stats, flags, (cudaStream_t) stream);
+}
+
+int drrt_trace_sdf(const float *rif, const float *sdf, int W, int H, int D, const float *pos,
+                   const float *vel, int64_t N, int layout, float h, float ds, float *xt,
+                   float *vt, int64_t *stats, unsigned flags, drrt_stream_t stream) {
+  if (!sdf) return fail(DRRT_ERR_INVALID_ARGUMENT, "sdf is NULL");
+  return trace_common(3, rif, sdf, W, H, D, pos, vel, nullptr, nullptr, N, layout, h, ds, xt, vt,
+                      nullptr, nullptr, stats, flags, (cudaStream_t) stream);
+}
+
+int drrt_trace_cable(const float *rif, int res, float radius, float length, const float *pos,
+                     const float *vel, const float *target, int64_t N, int layout, float ds,
+                     float *xt, float *vt, float *dist2, int64_t *stats, unsigned flags,
+                     drrt_stream_t stream) {
+  CableArgs a;
+  memset(&a, 0, sizeof a);
+  int rc = make_cable(a.cable, rif, res, radius, length);
+  if (rc) return rc;
+  if ((rc = check_rays(N, layout, ds))) return rc;
+  if (N == 0) return DRRT_OK;
+  if (!pos || !vel || !target || !xt || !vt || !dist2) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL ray buffer");
+  a.pos = pos; a.vel = vel; a.target = target; a.N = N; a.layout = layout; a.ds = ds;
+  a.max_steps = cap_cable(length, ds);
+  a.xt = xt; a.vt = vt; a.dist2 = dist2; a.stats = stats;
+  g_launches += launch_trace_cable((flags & DRRT_REFERENCE_ARITH) != 0, a, (cudaStream_t) stream);
+  return check_launch("trace_cable");
+}
+
+size_t drrt_backtrace_scratch_bytes(int64_t grid_elems, unsigned flags) {
+  if (!(flags & DRRT_DETERMINISTIC) || grid_elems <= 0) return 0;
+  return sizeof(unsigned long long) * (size_t) grid_elems + kFixedTail;
+}
+
+int drrt_backtrace(const float *rif, int W, int H, int D, const float *xt, const float *vt,
+                   const float *dx, const float *dv, int64_t N, int layout, float h, float ds,
+                   float *grad, void *scratch, int64_t *stats, unsigned flags,
+                   drrt_stream_t stream) {
+  return backtrace_common(false, rif, nullptr, W, H, D, xt, vt, dx, dv, N, layout, h, ds, grad,
+                          scratch, stats, flags, (cudaStream_t) stream);
+}
+
+int drrt_backtrace_sdf(const float *rif, const float *sdf, int W, int H, int D, const float *xt,
+                       const float *vt, const float *dx, const float *dv, int64_t N, int layout,
+                       float h, float ds, float *grad, void *scratch, int64_t *stats,
+                       unsigned flags, drrt_stream_t stream) {
+  if (!sdf) return fail(DRRT_ERR_INVALID_ARGUMENT, "sdf is NULL");
+  return backtrace_common(true, rif, sdf, W, H, D, xt, vt, dx, dv, N, layout, h, ds, grad, scratch,
+                          stats, flags, (cudaStream_t) stream);
+}
+
+int drrt_backtrace_cable(const float *rif, int res, float radius, float length, const float *xt,
+                         const float *vt, const float *dx, const float *dv, int64_t N, int layout,
+                         float ds, float *grad, void *scratch, int64_t *stats, unsigned flags,
+                         drrt_stream_t stream) {
+  cudaStream_t s = (cudaStream_t) stream;
+  CableArgs a;
+  memset(&a, 0, sizeof a);
+  int rc = make_cable(a.cable, rif, res, radius, length);
+  if (rc) return rc;
+  if ((rc = check_rays(N, layout, ds))) return rc;
+  if (!grad) return fail(DRRT_ERR_INVALID_ARGUMENT, "grad is NULL");
+  const bool det = (flags & DRRT_DETERMINISTIC) != 0;
+  const bool accumulate = (flags & DRRT_ACCUMULATE) != 0;
+  if (det && !scratch) return fail(DRRT_ERR_INVALID_ARGUMENT, "DRRT_DETERMINISTIC needs a scratch buffer");
+  if (!accumulate) CU_TRY(cudaMemsetAsync(grad, 0, sizeof(float) * (size_t) res, s));
+  if (N == 0) return DRRT_OK;
+  if (!xt || !vt || !dx || !dv) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL ray buffer");
+  a.pos = xt; a.vel = vt; a.dx = dx; a.dv = dv; a.N = N; a.layout = layout; a.ds = ds;
+  a.max_steps = cap_cable(length, ds);
+  a.stats = stats;
+  unsigned long long *fixed = nullptr;
+  unsigned *max_bits = nullptr;
+  if (det) {
+    fixed = (unsigned long long *) scratch;
+    max_bits = (unsigned *) ((char *) scratch + sizeof(unsigned long long) * (size_t) res);
+    CU_TRY(cudaMemsetAsync(scratch, 0, sizeof(unsigned long long) * (size_t) res + kFixedTail, s));
+    g_launches += launch_fixed_max(dx, dv, 3 * N, max_bits, s);
+  }
+  g_launches += launch_backtrace_cable((flags & DRRT_REFERENCE_ARITH) != 0, a, grad, fixed, max_bits, s);
+  if (det) g_launches += launch_fixed_to_float(fixed, max_bits, grad, res, accumulate, s);
+  return check_launch("backtrace_cable");
+}
+
+int drrt_volume_eval(const float *rif, int W, int H, int D, const float *pos, int64_t N,
+                     int layout, float h, float *n, float *grad, float *hess, unsigned flags,
+                     drrt_stream_t stream) {
+  GridP g;
+  int rc = make_grid(g, rif, W, H, D, h);
+  if (rc) return rc;
+  if ((rc = check_rays(N, layout, 1.0f))) return rc;
+  g_launches += launch_volume_eval(g, pos, N, layout, n, grad, hess, (flags & DRRT_REFERENCE_ARITH) != 0,
+                                   (cudaStream_t) stream);
+  return check_launch("volume_eval");
+}
+
+int drrt_volume_splat(float *data, int W, int H, int D, const float *pos, const float *val,
+                      const float *grad, int64_t N, int layout, float h, drrt_stream_t stream) {
+  GridP g;
+  int rc = make_grid(g, data, W, H, D, h);
+  if (rc) return rc;
+  if ((rc = check_rays(N, layout, 1.0f))) return rc;
+  g_launches += launch_volume_splat(g, data, pos, val, grad, N, layout, (cudaStream_t) stream);
+  return check_launch("volume_splat");
+}
+
+int drrt_cylinder_eval(const float *rif, int res, float radius, float length, const float *pos,
+                       int64_t N, int layout, float *n, float *grad, float *hess,
+                       drrt_stream_t stream) {
+  CableP c;
+  int rc = make_cable(c, rif, res, radius, length);
+  if (rc) return rc;
+  if ((rc = check_rays(N, layout, 1.0f))) return rc;
+  g_launches += launch_cylinder_eval(c, pos, N, layout, n, grad, hess, (cudaStream_t) stream);
+  return check_launch("cylinder_eval");
+}
+
+int drrt_cylinder_splat(float *data, int res, float radius, float length, const float *pos,
+                        const float *val, const float *grad, int64_t N, int layout,
+                        drrt_stream_t stream) {
+  CableP c;
+  int rc = make_cable(c, data, res, radius, length);
+  if (rc) return rc;
+  if ((rc = check_rays(N, layout, 1.0f))) return rc;
+  g_launches += launch_cylinder_splat(c, data, pos, val, grad, N, layout, (cudaStream_t) stream);
+  return check_launch("cylinder_splat");
+}
+
+}  // extern "C"

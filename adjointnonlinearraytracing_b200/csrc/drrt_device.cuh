@@ -1,0 +1,290 @@
+// Device-side building blocks of the eikonal tracer (sm_100a).
+//
+// Semantics follow the reference's volume / cylinder_volume classes
+// (reference src/volume.cpp, src/cylinder_volume.cpp); file:line citations sit
+// on each function.  Two arithmetic flavours, selected at compile time:
+//
+//   REF = true   the reference's exact operation order, every multiply/add a
+//                separately rounded IEEE operation (__fmul_rn/__fadd_rn are
+//                never contracted by nvcc) and FMA only where the reference
+//                writes fmadd.  Bit-identical to a float32 CPU evaluation.
+//   REF = false  the trilinear cell as a polynomial in the fractional
+//                coordinates, a0 + ax*wx + ... + axyz*wx*wy*wz, whose 8
+//                coefficients are cached in registers while the ray stays in
+//                the cell: 11 FMAs give n and grad n, 1 more the Hessian.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace drrt {
+
+struct GridP {
+  const float *data;
+  int W, H, D;
+  float h, rcp_h;
+  float hix, hiy, hiz;  // (res_k - 1) * h, src/volume.cpp:252-254
+};
+
+struct CableP {
+  const float *data;
+  int res;
+  float radius, length;
+  float h;   // radius / (res - 1), src/cylinder_volume.cpp:42
+  float r2;  // radius * radius
+};
+
+struct f3 {
+  float x, y, z;
+};
+
+__device__ __forceinline__ f3 ld3(const float *p, int64_t i, int64_t n, int layout) {
+  f3 r;
+  if (layout == 3) {
+    r.x = p[3 * i]; r.y = p[3 * i + 1]; r.z = p[3 * i + 2];
+  } else {
+    r.x = p[i]; r.y = p[n + i]; r.z = p[2 * n + i];
+  }
+  return r;
+}
+
+__device__ __forceinline__ void st3(float *p, int64_t i, int64_t n, int layout, f3 v) {
+  if (layout == 3) {
+    p[3 * i] = v.x; p[3 * i + 1] = v.y; p[3 * i + 2] = v.z;
+  } else {
+    p[i] = v.x; p[n + i] = v.y; p[2 * n + i] = v.z;
+  }
+}
+
+// strictly rounded helpers (no contraction)
+__device__ __forceinline__ float mul_(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add_(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub_(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float fma_(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+
+// volume::inbounds, src/volume.cpp:246-256
+__device__ __forceinline__ bool inbounds(const GridP &g, f3 p) {
+  return (p.x >= 0.f) & (p.y >= 0.f) & (p.z >= 0.f) & (p.x < g.hix) & (p.y < g.hiy) & (p.z < g.hiz);
+}
+
+// volume::escaped, src/volume.cpp:258-271
+__device__ __forceinline__ bool escaped(const GridP &g, f3 p, f3 v) {
+  bool ex = ((p.x < 0.f) & (v.x < 0.f)) | ((p.x >= g.hix) & (v.x > 0.f));
+  bool ey = ((p.y < 0.f) & (v.y < 0.f)) | ((p.y >= g.hiy) & (v.y > 0.f));
+  bool ez = ((p.z < 0.f) & (v.z < 0.f)) | ((p.z >= g.hiz) & (v.z > 0.f));
+  return ex | ey | ez;
+}
+
+// Cell lookup, src/volume.cpp:128-141: fractional weights from the UNCLAMPED
+// floor, both corner indices clamped to [0, res-1].
+struct CellIdx {
+  int cx, cy, cz;     // unclamped floor(p / h)
+  float wx, wy, wz;   // w0
+};
+
+__device__ __forceinline__ CellIdx cell_of(const GridP &g, f3 p) {
+  CellIdx c;
+  float px = mul_(p.x, g.rcp_h), py = mul_(p.y, g.rcp_h), pz = mul_(p.z, g.rcp_h);
+  float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
+  c.cx = (int) fx; c.cy = (int) fy; c.cz = (int) fz;
+  c.wx = sub_(px, fx); c.wy = sub_(py, fy); c.wz = sub_(pz, fz);
+  return c;
+}
+
+// The 8 flat corner indices in the reference's order 000 100 010 110 001 101 011
+// 111 (first digit = x), src/volume.cpp:134-141.
+__device__ __forceinline__ void corner_indices(const GridP &g, int cx, int cy, int cz, int idx[8]) {
+  int x0 = max(min(cx, g.W - 1), 0), x1 = max(min(cx + 1, g.W - 1), 0);
+  int y0 = max(min(cy, g.H - 1), 0), y1 = max(min(cy + 1, g.H - 1), 0);
+  int z0 = max(min(cz, g.D - 1), 0), z1 = max(min(cz + 1, g.D - 1), 0);
+  int r00 = (z0 * g.H + y0) * g.W, r10 = (z0 * g.H + y1) * g.W;
+  int r01 = (z1 * g.H + y0) * g.W, r11 = (z1 * g.H + y1) * g.W;
+  idx[0] = r00 + x0; idx[1] = r00 + x1; idx[2] = r10 + x0; idx[3] = r10 + x1;
+  idx[4] = r01 + x0; idx[5] = r01 + x1; idx[6] = r11 + x0; idx[7] = r11 + x1;
+}
+
+__device__ __forceinline__ void load_corners(const GridP &g, const int idx[8], float v[8]) {
+#pragma unroll
+  for (int k = 0; k < 8; ++k) v[k] = __ldg(g.data + idx[k]);
+}
+
+// ---------------------------------------------------------------------------
+// Reference-order arithmetic (REF = true)
+// ---------------------------------------------------------------------------
+
+// volume::eval_grad, src/volume.cpp:152-178, from already-gathered corners.
+__device__ __forceinline__ void eval_grad_ref(const GridP &g, const float v[8], float w0x, float w0y,
+                                              float w0z, float &n, f3 &nx) {
+  float w1x = sub_(1.0f, w0x), w1y = sub_(1.0f, w0y), w1z = sub_(1.0f, w0z);
+  float v000 = v[0], v100 = v[1], v010 = v[2], v110 = v[3];
+  float v001 = v[4], v101 = v[5], v011 = v[6], v111 = v[7];
+  float w000 = mul_(mul_(w1x, w1y), w1z), w100 = mul_(mul_(w0x, w1y), w1z);
+  float w010 = mul_(mul_(w1x, w0y), w1z), w110 = mul_(mul_(w0x, w0y), w1z);
+  float w001 = mul_(mul_(w1x, w1y), w0z), w101 = mul_(mul_(w0x, w1y), w0z);
+  float w011 = mul_(mul_(w1x, w0y), w0z), w111 = mul_(mul_(w0x, w0y), w0z);
+  float s = mul_(w000, v000);
+  s = add_(s, mul_(w100, v100)); s = add_(s, mul_(w010, v010)); s = add_(s, mul_(w110, v110));
+  s = add_(s, mul_(w001, v001)); s = add_(s, mul_(w101, v101)); s = add_(s, mul_(w011, v011));
+  s = add_(s, mul_(w111, v111));
+  n = s;
+#define DRRT_Q(va, wa, wb) mul_(mul_(va, wa), wb)
+#define DRRT_S4(a, b, c, d) add_(add_(add_(a, b), c), d)
+  float gx = sub_(DRRT_S4(DRRT_Q(v100, w1y, w1z), DRRT_Q(v101, w1y, w0z), DRRT_Q(v110, w0y, w1z), DRRT_Q(v111, w0y, w0z)),
+                  DRRT_S4(DRRT_Q(v000, w1y, w1z), DRRT_Q(v001, w1y, w0z), DRRT_Q(v010, w0y, w1z), DRRT_Q(v011, w0y, w0z)));
+  float gy = sub_(DRRT_S4(DRRT_Q(v010, w1x, w1z), DRRT_Q(v011, w1x, w0z), DRRT_Q(v110, w0x, w1z), DRRT_Q(v111, w0x, w0z)),
+                  DRRT_S4(DRRT_Q(v000, w1x, w1z), DRRT_Q(v001, w1x, w0z), DRRT_Q(v100, w0x, w1z), DRRT_Q(v101, w0x, w0z)));
+  float gz = sub_(DRRT_S4(DRRT_Q(v001, w1x, w1y), DRRT_Q(v011, w1x, w0y), DRRT_Q(v101, w0x, w1y), DRRT_Q(v111, w0x, w0y)),
+                  DRRT_S4(DRRT_Q(v000, w1x, w1y), DRRT_Q(v010, w1x, w0y), DRRT_Q(v100, w0x, w1y), DRRT_Q(v110, w0x, w0y)));
+#undef DRRT_Q
+#undef DRRT_S4
+  nx.x = mul_(gx, g.rcp_h); nx.y = mul_(gy, g.rcp_h); nx.z = mul_(gz, g.rcp_h);
+}
+
+// enoki lerp(a,b,t) = fmadd(b, t, fnmadd(a, t, a))
+__device__ __forceinline__ float lerp_ref(float a, float b, float t) { return fma_(b, t, fma_(-a, t, a)); }
+
+// volume::eval_hess, src/volume.cpp:79-98: (dxdy, dxdz, dydz), / h / h as two
+// multiplications by rcp(h).
+__device__ __forceinline__ f3 eval_hess_ref(const GridP &g, const float v[8], float w0x, float w0y,
+                                            float w0z) {
+  float v000 = v[0], v100 = v[1], v010 = v[2], v110 = v[3];
+  float v001 = v[4], v101 = v[5], v011 = v[6], v111 = v[7];
+  float dxdy = lerp_ref(add_(sub_(sub_(v110, v010), v100), v000), add_(sub_(sub_(v111, v011), v101), v001), w0z);
+  float dxdz = lerp_ref(add_(sub_(sub_(v101, v001), v100), v000), add_(sub_(sub_(v111, v011), v110), v010), w0y);
+  float dydz = lerp_ref(add_(sub_(sub_(v011, v001), v010), v000), add_(sub_(sub_(v111, v101), v110), v100), w0x);
+  f3 hm;
+  hm.x = mul_(mul_(dxdy, g.rcp_h), g.rcp_h);
+  hm.y = mul_(mul_(dxdz, g.rcp_h), g.rcp_h);
+  hm.z = mul_(mul_(dydz, g.rcp_h), g.rcp_h);
+  return hm;
+}
+
+// The 16 terms of volume::splat, src/volume.cpp:217-243 (no 1/h on the gradient
+// weights -- the reference's quirk, kept).
+__device__ __forceinline__ void splat_terms_ref(float val, f3 gr, float w0x, float w0y, float w0z,
+                                                float t[16]) {
+  float w1x = sub_(1.0f, w0x), w1y = sub_(1.0f, w0y), w1z = sub_(1.0f, w0z);
+  t[0] = mul_(mul_(mul_(val, w1x), w1y), w1z);
+  t[1] = mul_(mul_(mul_(val, w0x), w1y), w1z);
+  t[2] = mul_(mul_(mul_(val, w1x), w0y), w1z);
+  t[3] = mul_(mul_(mul_(val, w0x), w0y), w1z);
+  t[4] = mul_(mul_(mul_(val, w1x), w1y), w0z);
+  t[5] = mul_(mul_(mul_(val, w0x), w1y), w0z);
+  t[6] = mul_(mul_(mul_(val, w1x), w0y), w0z);
+  t[7] = mul_(mul_(mul_(val, w0x), w0y), w0z);
+  float gx = gr.x, gy = gr.y, gz = gr.z, mx = -gr.x;
+#define DRRT_P(a, b, c) mul_(mul_(a, b), c)
+  t[8]  = sub_(sub_(DRRT_P(mx, w1y, w1z), DRRT_P(gy, w1x, w1z)), DRRT_P(gz, w1x, w1y));
+  t[9]  = sub_(sub_(DRRT_P(gx, w1y, w1z), DRRT_P(gy, w0x, w1z)), DRRT_P(gz, w0x, w1y));
+  t[10] = sub_(add_(DRRT_P(mx, w0y, w1z), DRRT_P(gy, w1x, w1z)), DRRT_P(gz, w1x, w0y));
+  t[11] = sub_(add_(DRRT_P(gx, w0y, w1z), DRRT_P(gy, w0x, w1z)), DRRT_P(gz, w0x, w0y));
+  t[12] = add_(sub_(DRRT_P(mx, w1y, w0z), DRRT_P(gy, w1x, w0z)), DRRT_P(gz, w1x, w1y));
+  t[13] = add_(sub_(DRRT_P(gx, w1y, w0z), DRRT_P(gy, w0x, w0z)), DRRT_P(gz, w0x, w1y));
+  t[14] = add_(add_(DRRT_P(mx, w0y, w0z), DRRT_P(gy, w1x, w0z)), DRRT_P(gz, w1x, w0y));
+  t[15] = add_(add_(DRRT_P(gx, w0y, w0z), DRRT_P(gy, w0x, w0z)), DRRT_P(gz, w0x, w0y));
+#undef DRRT_P
+}
+
+// ---------------------------------------------------------------------------
+// Polynomial cell (REF = false)
+// ---------------------------------------------------------------------------
+struct CellPoly {
+  float a0, ax, ay, az, axy, axz, ayz, axyz;
+};
+
+__device__ __forceinline__ CellPoly make_poly(const float v[8]) {
+  CellPoly c;
+  c.a0 = v[0];
+  c.ax = v[1] - v[0];
+  c.ay = v[2] - v[0];
+  c.az = v[4] - v[0];
+  float bx = v[3] - v[2];  // x-difference on the y1 edge
+  float cxx = v[5] - v[4]; // x-difference on the z1 edge
+  float dxx = v[7] - v[6]; // x-difference on the y1 z1 edge
+  c.axy = bx - c.ax;
+  c.axz = cxx - c.ax;
+  c.ayz = (v[6] - v[4]) - c.ay;
+  c.axyz = (dxx - cxx) - c.axy;
+  return c;
+}
+
+// n, grad n (in cell units: multiply by rcp_h for world units) and the three
+// mixed second partials (cell units: multiply by rcp_h^2).
+__device__ __forceinline__ void eval_poly(const CellPoly &c, float wx, float wy, float wz, float &n,
+                                          f3 &g, f3 &hm) {
+  float pxy = fmaf(c.axyz, wz, c.axy);
+  float pxz = fmaf(c.axyz, wy, c.axz);
+  float pyz = fmaf(c.axyz, wx, c.ayz);
+  float tx = fmaf(c.axz, wz, c.ax);
+  float ty = fmaf(c.ayz, wz, c.ay);
+  float tz = fmaf(c.ayz, wy, c.az);
+  g.x = fmaf(pxy, wy, tx);
+  g.y = fmaf(pxy, wx, ty);
+  g.z = fmaf(pxz, wx, tz);
+  n = fmaf(wx, g.x, fmaf(wy, ty, fmaf(c.az, wz, c.a0)));
+  hm.x = pxy; hm.y = pxz; hm.z = pyz;
+}
+
+// Fused splat: contribution of (val, gr) to the 8 corners, i.e. term[k] +
+// term[8+k] of splat_terms_ref, factored as
+//   c_ijk = A_i * wy_j * wz_k + wx_i * (gy*s_j*wz_k + gz*s_k*wy_j),
+//   A_i = val*wx_i + s_i*gx,  s_0 = -1, s_1 = +1,  w_0 = 1 - w, w_1 = w.
+__device__ __forceinline__ void splat_accumulate(float val, f3 gr, float wx, float wy, float wz,
+                                                 float acc[8]) {
+  float ux = 1.0f - wx, uy = 1.0f - wy, uz = 1.0f - wz;
+  float A0 = fmaf(val, ux, -gr.x), A1 = fmaf(val, wx, gr.x);
+  float B00 = uy * uz, B10 = wy * uz, B01 = uy * wz, B11 = wy * wz;
+  float gyuz = gr.y * uz, gywz = gr.y * wz, gzuy = gr.z * uy, gzwy = gr.z * wy;
+  float C00 = -gyuz - gzuy, C10 = gyuz - gzwy, C01 = gzuy - gywz, C11 = gywz + gzwy;
+  acc[0] = fmaf(ux, C00, fmaf(A0, B00, acc[0]));
+  acc[1] = fmaf(wx, C00, fmaf(A1, B00, acc[1]));
+  acc[2] = fmaf(ux, C10, fmaf(A0, B10, acc[2]));
+  acc[3] = fmaf(wx, C10, fmaf(A1, B10, acc[3]));
+  acc[4] = fmaf(ux, C01, fmaf(A0, B01, acc[4]));
+  acc[5] = fmaf(wx, C01, fmaf(A1, B01, acc[5]));
+  acc[6] = fmaf(ux, C11, fmaf(A0, B11, acc[6]));
+  acc[7] = fmaf(wx, C11, fmaf(A1, B11, acc[7]));
+}
+
+// ---------------------------------------------------------------------------
+// Gradient accumulation back ends
+// ---------------------------------------------------------------------------
+// float atomics (red.global.add.f32) or 64-bit fixed point for the
+// deterministic mode: integer addition is associative, so the sum is
+// independent of the order in which threads arrive.
+struct AccumFloat {
+  typedef float T;
+  float *dst;
+  __device__ __forceinline__ void prepare() {}
+  __device__ __forceinline__ float q(float v) const { return v; }
+  __device__ __forceinline__ void add(int idx, float v) const { atomicAdd(dst + idx, v); }
+};
+
+struct AccumFixed {
+  typedef unsigned long long T;
+  unsigned long long *dst;
+  const unsigned *max_bits;  // bit pattern of max(|dx|,|dv|) over the batch (device)
+  float scale;               // set by prepare(): a power of two
+  // scale = 2^(34 - e) with max = m * 2^e, m in [0.5, 1): every thread derives the
+  // same value, contributions keep ~34 bits below the largest seed and ~29 bits of
+  // headroom above it before the int64 sum could overflow.
+  static __device__ __forceinline__ float scale_from_bits(unsigned bits) {
+    float m = __uint_as_float(bits);
+    if (!(m > 0.f) || !(m < 3.0e38f)) return 1.0f;
+    int e;
+    frexpf(m, &e);
+    return exp2f((float) (34 - e));
+  }
+  __device__ __forceinline__ void prepare() { scale = scale_from_bits(*max_bits); }
+  __device__ __forceinline__ unsigned long long q(float v) const {
+    return (unsigned long long) __float2ll_rn(v * scale);
+  }
+  __device__ __forceinline__ void add(int idx, float v) const { atomicAdd(dst + idx, q(v)); }
+};
+
+__device__ __forceinline__ int64_t warp_sum_i64(int64_t v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+}  // namespace drrt

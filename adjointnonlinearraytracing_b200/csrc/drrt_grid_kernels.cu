@@ -1,0 +1,361 @@
+// Forward eikonal trace and adjoint backtrace through a regular IOR grid.
+//
+// One ray per thread, the whole integration loop in registers, per-ray exit:
+// the reference instead launches one JIT kernel + one host-synchronising
+// all()/none() reduction per step (reference src/tracer.cpp:82, :426) and
+// streams every ray's state through global memory each step.
+//
+// Per-ray early exit is exact for trace / trace_plane / trace_sdf / backtrace*:
+// once a ray is `escaped` (forward) or not `active` (adjoint) none of its
+// outputs can change again (gathers are masked to 0 outside, so it flies
+// straight away from a convex box).  trace_target is the exception -- see
+// trace_target_tail_kernel.
+#include "drrt_device.cuh"
+#include "drrt_launch.h"
+
+namespace drrt {
+
+enum { K_PLAIN = 0, K_PLANE = 1, K_TARGET = 2, K_SDF = 3 };
+
+// Register cache of the cell a ray is in.  REF keeps the 8 corner values,
+// otherwise the 8 polynomial coefficients.
+template <bool REF>
+struct CellCache;
+
+template <>
+struct CellCache<true> {
+  int cx = INT_MIN, cy = 0, cz = 0;
+  float v[8];
+  __device__ __forceinline__ void refill(const GridP &g, const int idx[8]) { load_corners(g, idx, v); }
+  __device__ __forceinline__ void eval(const GridP &g, const CellIdx &c, float &n, f3 &nx, f3 *hm) const {
+    eval_grad_ref(g, v, c.wx, c.wy, c.wz, n, nx);
+    if (hm) *hm = eval_hess_ref(g, v, c.wx, c.wy, c.wz);
+  }
+};
+
+template <>
+struct CellCache<false> {
+  int cx = INT_MIN, cy = 0, cz = 0;
+  CellPoly p;
+  __device__ __forceinline__ void refill(const GridP &g, const int idx[8]) {
+    float v[8];
+    load_corners(g, idx, v);
+    p = make_poly(v);
+  }
+  // nx and hm are returned in world units
+  __device__ __forceinline__ void eval(const GridP &g, const CellIdx &c, float &n, f3 &nx, f3 *hm) const {
+    f3 gg, hh;
+    eval_poly(p, c.wx, c.wy, c.wz, n, gg, hh);
+    nx.x = gg.x * g.rcp_h; nx.y = gg.y * g.rcp_h; nx.z = gg.z * g.rcp_h;
+    if (hm) {
+      float r2 = g.rcp_h * g.rcp_h;
+      hm->x = hh.x * r2; hm->y = hh.y * r2; hm->z = hh.z * r2;
+    }
+  }
+};
+
+template <bool REF>
+__device__ __forceinline__ bool cell_changed(const CellCache<REF> &cc, const CellIdx &c) {
+  return (c.cx != cc.cx) | (c.cy != cc.cy) | (c.cz != cc.cz);
+}
+
+// Trilinear value only (sdf lookups), src/volume.cpp:162-163 under the caller's mask.
+template <bool REF>
+__device__ __forceinline__ float eval_value(const GridP &g, CellCache<REF> &cc, f3 x) {
+  CellIdx c = cell_of(g, x);
+  if (cell_changed(cc, c)) {
+    int idx[8];
+    corner_indices(g, c.cx, c.cy, c.cz, idx);
+    cc.refill(g, idx);
+    cc.cx = c.cx; cc.cy = c.cy; cc.cz = c.cz;
+  }
+  float n; f3 nx;
+  cc.eval(g, c, n, nx, nullptr);
+  return n;
+}
+
+__device__ __forceinline__ float dist2_ref(f3 x, f3 t) {
+  float dx = sub_(x.x, t.x), dy = sub_(x.y, t.y), dz = sub_(x.z, t.z);
+  return fma_(dz, dz, fma_(dy, dy, mul_(dx, dx)));  // squared_norm: mul, fmadd, fmadd
+}
+
+// ---------------------------------------------------------------------------
+// Forward: Tracer::trace (src/tracer.cpp:35-100), trace_plane (:102-172),
+// trace_target (:174-242, per-ray part), trace_sdf (:244-310).
+// ---------------------------------------------------------------------------
+template <int KIND, bool REF>
+__global__ void __launch_bounds__(kTraceThreads) trace_kernel(TraceArgs a) {
+  const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  const bool valid = r < a.N;
+  int64_t steps = 0;
+  int not_exited = 0;
+  if (valid) {
+    const GridP g = a.grid;
+    const float ds = a.ds;
+    f3 x = ld3(a.pos, r, a.N, a.layout), v = ld3(a.vel, r, a.N, a.layout);
+    f3 xt = x, vt = v;
+    f3 aux0 = {0, 0, 0}, aux1 = {0, 0, 0};
+    float best = 0.f;
+    if (KIND == K_PLANE) { aux0 = ld3(a.aux0, r, a.N, a.layout); aux1 = ld3(a.aux1, r, a.N, a.layout); }
+    if (KIND == K_TARGET) { aux0 = ld3(a.aux0, r, a.N, a.layout); best = dist2_ref(x, aux0); }
+    bool inside = inbounds(g, x);  // :61
+    bool esc = false;
+    CellCache<REF> cc;
+    CellCache<REF> sc;  // sdf grid (K_SDF only)
+    GridP sg = g;
+    sg.data = a.sdf;
+    int i = 0;
+    for (; i < a.max_steps; ++i) {
+      if (inside) {  // masked gather: outside lanes see n = 0, grad n = 0 and fly straight
+        CellIdx c = cell_of(g, x);
+        if (cell_changed(cc, c)) {
+          int idx[8];
+          corner_indices(g, c.cx, c.cy, c.cz, idx);
+          cc.refill(g, idx);
+          cc.cx = c.cx; cc.cy = c.cy; cc.cz = c.cz;
+        }
+        float n; f3 nx;
+        cc.eval(g, c, n, nx, nullptr);
+        float dsn = REF ? mul_(ds, n) : ds * n;
+        v.x = fmaf(dsn, nx.x, v.x); v.y = fmaf(dsn, nx.y, v.y); v.z = fmaf(dsn, nx.z, v.z);  // :70
+      }
+      x.x = fmaf(ds, v.x, x.x); x.y = fmaf(ds, v.y, x.y); x.z = fmaf(ds, v.z, x.z);  // :71
+      ++steps;
+      const bool inb = inbounds(g, x);
+      bool cur_inside = inb;  // :73
+      if (KIND == K_PLANE) {  // :144-145
+        float dd = mul_(sub_(x.x, aux0.x), aux1.x);
+        dd = fma_(sub_(x.y, aux0.y), aux1.y, dd);
+        dd = fma_(sub_(x.z, aux0.z), aux1.z, dd);
+        cur_inside = inb & !(dd > 0.f);
+      }
+      if (KIND == K_SDF) {  // :287-288, evaluated under the previous `inside`
+        cur_inside = inside ? (eval_value<REF>(sg, sc, x) < 0.f) : false;
+      }
+      const bool cross = inside & !cur_inside;  // :74
+      if (KIND == K_TARGET) {  // :216-227
+        float cur = dist2_ref(x, aux0);
+        if (cur < best) { xt = x; vt = v; best = cur; }
+      } else if (cross) {  // :79-80
+        xt = x; vt = v;
+      }
+      esc = cross | (!inb && escaped(g, x, v));  // :75-76 (escaped() implies !inbounds)
+      inside = cur_inside;  // :86
+      if (esc) { ++i; break; }
+    }
+    if (!esc) {
+      not_exited = 1;
+      if (KIND == K_PLAIN || KIND == K_PLANE) xt = x;  // :95, :167 (vt keeps the launch value)
+    }
+    st3(a.xt, r, a.N, a.layout, xt);
+    st3(a.vt, r, a.N, a.layout, vt);
+    if (KIND == K_PLANE) a.not_escaped[r] = esc ? 0 : 1;  // :171
+    if (KIND == K_TARGET) {
+      a.dist2[r] = best;
+      // state for the batch-coupled tail
+      st3(a.tail_x, r, a.N, DRRT_LAYOUT_SOA, x);
+      st3(a.tail_v, r, a.N, DRRT_LAYOUT_SOA, v);
+      a.tail_iters[r] = i;
+      atomicMax(a.tail_max_iters, i);
+    }
+  }
+  if (a.stats) {
+    steps = warp_sum_i64(steps);
+    int ne = __reduce_add_sync(0xffffffffu, not_exited);
+    if ((threadIdx.x & 31) == 0) {
+      if (steps) atomicAdd((unsigned long long *) a.stats, (unsigned long long) steps);
+      if (ne) atomicAdd((unsigned long long *) a.stats + 1, (unsigned long long) ne);
+    }
+  }
+}
+
+// trace_target couples rays: the reference keeps testing every ray for a new
+// closest approach until the whole batch has escaped (src/tracer.cpp:216-231),
+// so an already-escaped ray's result depends on how long the slowest ray keeps
+// the loop alive.  After escape a ray is outside the box, its gathers are masked
+// to zero and it moves on the straight line x += ds*v; this kernel replays
+// exactly those remaining iterations (up to the batch-wide count found by
+// trace_kernel<K_TARGET>) and keeps updating the closest sample.
+__global__ void __launch_bounds__(kTraceThreads) trace_target_tail_kernel(TraceArgs a) {
+  const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= a.N) return;
+  const int total = *a.tail_max_iters;
+  int i = a.tail_iters[r];
+  if (i >= total) return;
+  const float ds = a.ds;
+  f3 x = ld3(a.tail_x, r, a.N, DRRT_LAYOUT_SOA), v = ld3(a.tail_v, r, a.N, DRRT_LAYOUT_SOA);
+  f3 t = ld3(a.aux0, r, a.N, a.layout);
+  float best = a.dist2[r];
+  bool upd = false;
+  f3 bx = x;
+  for (; i < total; ++i) {
+    x.x = fmaf(ds, v.x, x.x); x.y = fmaf(ds, v.y, x.y); x.z = fmaf(ds, v.z, x.z);
+    float cur = dist2_ref(x, t);
+    if (cur < best) { best = cur; bx = x; upd = true; }
+  }
+  if (upd) {
+    st3(a.xt, r, a.N, a.layout, bx);
+    st3(a.vt, r, a.N, a.layout, v);
+    a.dist2[r] = best;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Adjoint: Tracer::backtrace (src/tracer.cpp:384-440), backtrace_sdf (:443-509).
+// The ray is re-integrated backwards from its stored exit state; no tape.
+//
+// Gradient splat.  REF: the reference's 16 terms, one atomic each
+// (src/volume.cpp:217-243).  Otherwise: the two terms per corner are fused
+// (8 values), and those 8 values are ACCUMULATED IN REGISTERS for as long as
+// the ray stays in the same cell; they are flushed with 8 atomics only when the
+// ray moves to another cell (ds = h/2 gives ~2 steps per cell, so ~4 atomics per
+// step instead of 16).
+// ---------------------------------------------------------------------------
+template <bool SDF, bool REF, class Accum>
+__global__ void __launch_bounds__(kAdjThreads) backtrace_kernel(AdjArgs a, Accum out_in) {
+  Accum out = out_in;
+  out.prepare();
+  const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  const bool valid = r < a.N;
+  int64_t steps = 0;
+  if (valid) {
+    const GridP g = a.grid;
+    const float ds = a.ds;
+    f3 x = ld3(a.xt, r, a.N, a.layout), v = ld3(a.vt, r, a.N, a.layout);
+    f3 la = ld3(a.dx, r, a.N, a.layout), mu = ld3(a.dv, r, a.N, a.layout);
+    mu.x = add_(mu.x, mul_(ds, la.x)); mu.y = add_(mu.y, mul_(ds, la.y)); mu.z = add_(mu.z, mul_(ds, la.z));  // :410
+    f3 nv = {-v.x, -v.y, -v.z};
+    bool active = !escaped(g, x, nv);  // :413-414
+    CellCache<REF> cc;
+    CellCache<REF> sc;
+    GridP sg = g;
+    sg.data = a.sdf;
+    bool outside = false;
+    if (SDF) {  // :476-477
+      float dist = active ? eval_value<REF>(sg, sc, x) : 0.f;
+      outside = dist >= 0.f;
+    }
+    int idx[8];
+    float acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { acc[k] = 0.f; idx[k] = 0; }
+    bool have = false;
+    for (int i = 0; active && i < a.max_steps; ++i) {
+      x.x = fmaf(-ds, v.x, x.x); x.y = fmaf(-ds, v.y, x.y); x.z = fmaf(-ds, v.z, x.z);  // :420
+      CellIdx c = cell_of(g, x);
+      if (cell_changed(cc, c)) {
+        if (!REF && have) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) { out.add(idx[k], acc[k]); acc[k] = 0.f; }
+          have = false;
+        }
+        corner_indices(g, c.cx, c.cy, c.cz, idx);
+        cc.refill(g, idx);
+        cc.cx = c.cx; cc.cy = c.cy; cc.cz = c.cz;
+      }
+      float n; f3 nx, hm;
+      cc.eval(g, c, n, nx, &hm);  // :421-422 (same 8 voxels serve grad and Hessian)
+      float mdsn = REF ? mul_(-ds, n) : -ds * n;
+      v.x = fmaf(mdsn, nx.x, v.x); v.y = fmaf(mdsn, nx.y, v.y); v.z = fmaf(mdsn, nx.z, v.z);  // :423
+      ++steps;
+      nv.x = -v.x; nv.y = -v.y; nv.z = -v.z;
+      active = inbounds(g, x) || !escaped(g, x, nv);  // :425
+      if (SDF) {  // :488-497
+        float dist = eval_value<REF>(sg, sc, x);
+        bool now_out = dist >= 0.f;
+        active = active & !(!outside & now_out);
+        outside = now_out;
+      }
+      if (!active) break;  // :426 per ray
+      if (REF) {
+        float dn = fma_(mu.z, nx.z, fma_(mu.y, nx.y, mul_(mu.x, nx.x)));  // :430
+        f3 dnx = {mul_(mul_(n, mu.x), ds), mul_(mul_(n, mu.y), ds), mul_(mul_(n, mu.z), ds)};  // :431-432
+        float t[16];
+        splat_terms_ref(mul_(dn, ds), dnx, c.wx, c.wy, c.wz, t);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) out.add(idx[k & 7], t[k]);
+        // :434  la += ds * (dn * nx + (n * Hess) * mu), matrix.h:170-178 column sums
+        float nhxy = mul_(n, hm.x), nhxz = mul_(n, hm.y), nhyz = mul_(n, hm.z);
+        float h0 = fma_(nhxz, mu.z, mul_(nhxy, mu.y));
+        float h1 = fma_(nhyz, mu.z, mul_(nhxy, mu.x));
+        float h2 = fma_(nhyz, mu.y, mul_(nhxz, mu.x));
+        la.x = add_(la.x, mul_(ds, add_(mul_(dn, nx.x), h0)));
+        la.y = add_(la.y, mul_(ds, add_(mul_(dn, nx.y), h1)));
+        la.z = add_(la.z, mul_(ds, add_(mul_(dn, nx.z), h2)));
+        mu.x = add_(mu.x, mul_(ds, la.x)); mu.y = add_(mu.y, mul_(ds, la.y)); mu.z = add_(mu.z, mul_(ds, la.z));  // :435
+      } else {
+        float dn = fmaf(mu.z, nx.z, fmaf(mu.y, nx.y, mu.x * nx.x));
+        float nds = n * ds;
+        f3 dnx = {nds * mu.x, nds * mu.y, nds * mu.z};
+        splat_accumulate(dn * ds, dnx, c.wx, c.wy, c.wz, acc);
+        have = true;
+        float nhxy = n * hm.x, nhxz = n * hm.y, nhyz = n * hm.z;
+        float h0 = fmaf(nhxz, mu.z, nhxy * mu.y);
+        float h1 = fmaf(nhyz, mu.z, nhxy * mu.x);
+        float h2 = fmaf(nhyz, mu.y, nhxz * mu.x);
+        la.x = fmaf(ds, fmaf(dn, nx.x, h0), la.x);
+        la.y = fmaf(ds, fmaf(dn, nx.y, h1), la.y);
+        la.z = fmaf(ds, fmaf(dn, nx.z, h2), la.z);
+        mu.x = fmaf(ds, la.x, mu.x); mu.y = fmaf(ds, la.y, mu.y); mu.z = fmaf(ds, la.z, mu.z);
+      }
+    }
+    if (!REF && have) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) out.add(idx[k], acc[k]);
+    }
+  }
+  if (a.stats) {
+    steps = warp_sum_i64(steps);
+    if ((threadIdx.x & 31) == 0 && steps) atomicAdd((unsigned long long *) a.stats, (unsigned long long) steps);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Launchers
+// ---------------------------------------------------------------------------
+static inline unsigned blocks_for(int64_t n, int threads) { return (unsigned) ((n + threads - 1) / threads); }
+
+template <int KIND>
+static void launch_trace_kind(bool ref, const TraceArgs &a, cudaStream_t s) {
+  unsigned nb = blocks_for(a.N, kTraceThreads);
+  if (ref) trace_kernel<KIND, true><<<nb, kTraceThreads, 0, s>>>(a);
+  else trace_kernel<KIND, false><<<nb, kTraceThreads, 0, s>>>(a);
+}
+
+int launch_trace(int kind, bool ref_arith, const TraceArgs &a, cudaStream_t s) {
+  if (a.N <= 0) return 0;
+  switch (kind) {
+    case K_PLAIN: launch_trace_kind<K_PLAIN>(ref_arith, a, s); return 1;
+    case K_PLANE: launch_trace_kind<K_PLANE>(ref_arith, a, s); return 1;
+    case K_SDF: launch_trace_kind<K_SDF>(ref_arith, a, s); return 1;
+    case K_TARGET:
+      launch_trace_kind<K_TARGET>(ref_arith, a, s);
+      trace_target_tail_kernel<<<blocks_for(a.N, kTraceThreads), kTraceThreads, 0, s>>>(a);
+      return 2;
+  }
+  return 0;
+}
+
+template <bool SDF, class Accum>
+static void launch_backtrace_acc(bool ref, const AdjArgs &a, Accum acc, cudaStream_t s) {
+  unsigned nb = blocks_for(a.N, kAdjThreads);
+  if (ref) backtrace_kernel<SDF, true, Accum><<<nb, kAdjThreads, 0, s>>>(a, acc);
+  else backtrace_kernel<SDF, false, Accum><<<nb, kAdjThreads, 0, s>>>(a, acc);
+}
+
+int launch_backtrace(bool sdf, bool ref_arith, const AdjArgs &a, float *grad,
+                     unsigned long long *fixed, const unsigned *fixed_max_bits, cudaStream_t s) {
+  if (a.N <= 0) return 0;
+  if (fixed) {
+    AccumFixed acc{fixed, fixed_max_bits, 1.0f};
+    if (sdf) launch_backtrace_acc<true>(ref_arith, a, acc, s);
+    else launch_backtrace_acc<false>(ref_arith, a, acc, s);
+  } else {
+    AccumFloat acc{grad};
+    if (sdf) launch_backtrace_acc<true>(ref_arith, a, acc, s);
+    else launch_backtrace_acc<false>(ref_arith, a, acc, s);
+  }
+  return 1;
+}
+
+}  // namespace drrt

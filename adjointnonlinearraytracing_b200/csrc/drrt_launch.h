@@ -1,0 +1,84 @@
+// Host-visible argument blocks and launchers shared by the kernel translation
+// units and the C ABI (drrt_capi.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <limits.h>
+#include <stdint.h>
+
+#include "drrt_device.cuh"
+
+#define DRRT_LAYOUT_SOA 1
+#define DRRT_LAYOUT_AOS 3
+
+namespace drrt {
+
+constexpr int kTraceThreads = 128;
+constexpr int kAdjThreads = 128;
+
+struct TraceArgs {
+  GridP grid;
+  const float *sdf;
+  const float *pos, *vel;
+  const float *aux0, *aux1;  // plane origin / normal, or target
+  int64_t N;
+  int layout;
+  float ds;
+  int max_steps;
+  float *xt, *vt;
+  uint8_t *not_escaped;
+  float *dist2;
+  int64_t *stats;
+  // trace_target tail state (SoA scratch)
+  float *tail_x, *tail_v;
+  int *tail_iters, *tail_max_iters;
+};
+
+struct AdjArgs {
+  GridP grid;
+  const float *sdf;
+  const float *xt, *vt, *dx, *dv;
+  int64_t N;
+  int layout;
+  float ds;
+  int max_steps;
+  int64_t *stats;
+};
+
+struct CableArgs {
+  CableP cable;
+  const float *pos, *vel, *target;  // adjoint: xt, vt, dx(=target slot unused)
+  const float *dx, *dv;
+  int64_t N;
+  int layout;
+  float ds;
+  int max_steps;
+  float *xt, *vt, *dist2;
+  int64_t *stats;
+};
+
+// kind: 0 plain, 1 plane, 2 target, 3 sdf.  Returns the number of kernels launched.
+int launch_trace(int kind, bool ref_arith, const TraceArgs &a, cudaStream_t s);
+int launch_backtrace(bool sdf, bool ref_arith, const AdjArgs &a, float *grad,
+                     unsigned long long *fixed, const unsigned *fixed_max_bits, cudaStream_t s);
+int launch_trace_cable(bool ref_arith, const CableArgs &a, cudaStream_t s);
+int launch_backtrace_cable(bool ref_arith, const CableArgs &a, float *grad,
+                           unsigned long long *fixed, const unsigned *fixed_max_bits,
+                           cudaStream_t s);
+
+// deterministic mode helpers
+int launch_fixed_max(const float *dx, const float *dv, int64_t n3, unsigned *max_bits,
+                     cudaStream_t s);
+int launch_fixed_to_float(const unsigned long long *fixed, const unsigned *max_bits, float *grad,
+                          int64_t G, bool accumulate, cudaStream_t s);
+
+// volume probes
+int launch_volume_eval(const GridP &g, const float *pos, int64_t N, int layout, float *n,
+                       float *grad, float *hess, bool ref_arith, cudaStream_t s);
+int launch_volume_splat(const GridP &g, float *data, const float *pos, const float *val,
+                        const float *grad, int64_t N, int layout, cudaStream_t s);
+int launch_cylinder_eval(const CableP &c, const float *pos, int64_t N, int layout, float *n,
+                         float *grad, float *hess, cudaStream_t s);
+int launch_cylinder_splat(const CableP &c, float *data, const float *pos, const float *val,
+                          const float *grad, int64_t N, int layout, cudaStream_t s);
+
+}  // namespace drrt

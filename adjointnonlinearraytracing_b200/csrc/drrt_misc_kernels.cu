@@ -1,0 +1,113 @@
+// Small helper kernels: deterministic-mode fixed-point plumbing and the
+// single-evaluation probes of the volume primitives used by the parity tests.
+#include "drrt_device.cuh"
+#include "drrt_launch.h"
+
+namespace drrt {
+
+// max(|dx|, |dv|) over the batch as a float bit pattern (non-negative floats
+// order like unsigned integers), consumed by AccumFixed::prepare().
+__global__ void fixed_max_kernel(const float *dx, const float *dv, int64_t n3, unsigned *max_bits) {
+  unsigned m = 0;
+  for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n3;
+       i += (int64_t) gridDim.x * blockDim.x) {
+    m = max(m, __float_as_uint(fabsf(dx[i])));
+    m = max(m, __float_as_uint(fabsf(dv[i])));
+  }
+  m = __reduce_max_sync(0xffffffffu, m);
+  if ((threadIdx.x & 31) == 0 && m) atomicMax(max_bits, m);
+}
+
+__global__ void fixed_to_float_kernel(const unsigned long long *fixed, const unsigned *max_bits,
+                                      float *grad, int64_t G, bool accumulate) {
+  const float inv = 1.0f / AccumFixed::scale_from_bits(*max_bits);
+  for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < G;
+       i += (int64_t) gridDim.x * blockDim.x) {
+    // int64 -> double -> scaled float: a single rounding to float at the end
+    float v = (float) ((double) (long long) fixed[i] * (double) inv);
+    grad[i] = accumulate ? grad[i] + v : v;
+  }
+}
+
+int launch_fixed_max(const float *dx, const float *dv, int64_t n3, unsigned *max_bits,
+                     cudaStream_t s) {
+  if (n3 <= 0) return 0;
+  int nb = (int) ((n3 + 1023) / 1024);
+  if (nb > 148 * 8) nb = 148 * 8;
+  fixed_max_kernel<<<nb, 256, 0, s>>>(dx, dv, n3, max_bits);
+  return 1;
+}
+
+int launch_fixed_to_float(const unsigned long long *fixed, const unsigned *max_bits, float *grad,
+                          int64_t G, bool accumulate, cudaStream_t s) {
+  if (G <= 0) return 0;
+  int nb = (int) ((G + 1023) / 1024);
+  if (nb > 148 * 8) nb = 148 * 8;
+  fixed_to_float_kernel<<<nb, 256, 0, s>>>(fixed, max_bits, grad, G, accumulate);
+  return 1;
+}
+
+// ---------------------------------------------------------------------------
+// Probes
+// ---------------------------------------------------------------------------
+template <bool REF>
+__global__ void volume_eval_kernel(GridP g, const float *pos, int64_t N, int layout, float *n,
+                                   float *grad, float *hess) {
+  const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= N) return;
+  f3 p = ld3(pos, r, N, layout);
+  CellIdx c = cell_of(g, p);
+  int idx[8];
+  float v[8];
+  corner_indices(g, c.cx, c.cy, c.cz, idx);
+  load_corners(g, idx, v);
+  float nn; f3 nx, hm;
+  if (REF) {
+    eval_grad_ref(g, v, c.wx, c.wy, c.wz, nn, nx);
+    hm = eval_hess_ref(g, v, c.wx, c.wy, c.wz);
+  } else {
+    CellPoly cp = make_poly(v);
+    f3 gg, hh;
+    eval_poly(cp, c.wx, c.wy, c.wz, nn, gg, hh);
+    float r2 = g.rcp_h * g.rcp_h;
+    nx.x = gg.x * g.rcp_h; nx.y = gg.y * g.rcp_h; nx.z = gg.z * g.rcp_h;
+    hm.x = hh.x * r2; hm.y = hh.y * r2; hm.z = hh.z * r2;
+  }
+  n[r] = nn;
+  st3(grad, r, N, layout, nx);
+  st3(hess, r, N, layout, hm);
+}
+
+// volume::splat, src/volume.cpp:182-244 (fused form; the order of the float
+// atomics is not the CPU's serial order).
+__global__ void volume_splat_kernel(GridP g, float *data, const float *pos, const float *val,
+                                    const float *grad, int64_t N, int layout) {
+  const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= N) return;
+  f3 p = ld3(pos, r, N, layout), gr = ld3(grad, r, N, layout);
+  CellIdx c = cell_of(g, p);
+  int idx[8];
+  corner_indices(g, c.cx, c.cy, c.cz, idx);
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  splat_accumulate(val[r], gr, c.wx, c.wy, c.wz, acc);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) atomicAdd(data + idx[k], acc[k]);
+}
+
+int launch_volume_eval(const GridP &g, const float *pos, int64_t N, int layout, float *n,
+                       float *grad, float *hess, bool ref_arith, cudaStream_t s) {
+  if (N <= 0) return 0;
+  unsigned nb = (unsigned) ((N + 127) / 128);
+  if (ref_arith) volume_eval_kernel<true><<<nb, 128, 0, s>>>(g, pos, N, layout, n, grad, hess);
+  else volume_eval_kernel<false><<<nb, 128, 0, s>>>(g, pos, N, layout, n, grad, hess);
+  return 1;
+}
+
+int launch_volume_splat(const GridP &g, float *data, const float *pos, const float *val,
+                        const float *grad, int64_t N, int layout, cudaStream_t s) {
+  if (N <= 0) return 0;
+  volume_splat_kernel<<<(unsigned) ((N + 127) / 128), 128, 0, s>>>(g, data, pos, val, grad, N, layout);
+  return 1;
+}
+
+}  // namespace drrt

@@ -1,0 +1,177 @@
+/*
+ * drrt_b200.h -- C ABI of libdrrt_b200.so: the eikonal ray tracer and its adjoint
+ * as hand-written sm_100a CUDA kernels.
+ *
+ * Each entry point replaces one method of the reference's pybind11 classes
+ * drrt.TracerC / TracerD / TracerS (reference src/drrt.cpp:28-58; C++ signatures
+ * include/tracer.h:15-89).  Argument order follows the reference method; enoki
+ * array arguments become plain pointers + sizes.
+ *
+ * Conventions
+ *   - float32 everywhere; the grid is flat, idx = (z*H + y)*W + x with
+ *     (W,H,D) = the `res` triple the reference passes (src/volume.cpp:134).
+ *   - Ray vectors: `layout` = DRRT_AOS for (N,3) row-major (what torch hands to
+ *     core/tracer.py) or DRRT_SOA for [3][N] (enoki's internal layout).
+ *   - Functions without the `_host` suffix take DEVICE pointers and enqueue work
+ *     on `stream` (a cudaStream_t; NULL = legacy default stream) without
+ *     synchronising.  The caller owns every buffer.
+ *   - `_host` functions take HOST pointers (pinned or pageable), copy in, run,
+ *     copy out and synchronise before returning.
+ *   - Return value: DRRT_OK or a negative error code; drrt_last_error() gives the
+ *     message of the calling thread's last failure.  The messages for size /
+ *     resolution mismatches are the reference's (src/volume.cpp:28,37,115,124).
+ *   - `stats` (nullable, device pointer for device entry points, host pointer for
+ *     `_host` ones) receives two int64: [0] += live ray-steps integrated,
+ *     [1] += rays that never exited (the reference only prints
+ *     "failed to exit all rays", src/tracer.cpp:89-96).  Device stats are
+ *     accumulated, not overwritten: zero them yourself.
+ */
+#ifndef DRRT_B200_H
+#define DRRT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DRRT_ABI_VERSION 1
+
+typedef void *drrt_stream_t; /* cudaStream_t */
+
+enum {
+  DRRT_OK = 0,
+  DRRT_ERR_INVALID_ARGUMENT = -1,
+  DRRT_ERR_RESOLUTION = -2, /* "Resolution doesn't match data" / "volume: invalid resolution!" */
+  DRRT_ERR_CUDA = -3,
+  DRRT_ERR_NCCL = -4
+};
+
+enum { DRRT_SOA = 1, DRRT_AOS = 3 };
+
+/* flags (bitwise or) */
+enum {
+  /* Arithmetic in the reference's exact operation order with no FMA contraction
+   * (bit-identical ray endpoints to a float32 CPU evaluation of the reference
+   * formulas).  Default is the factored per-cell polynomial form, which is
+   * algebraically identical and ~2x cheaper but rounds differently. */
+  DRRT_REFERENCE_ARITH = 1u << 0,
+  /* Adjoint only: accumulate the gradient in 64-bit fixed point so the result is
+   * bit-stable from run to run regardless of atomic ordering. */
+  DRRT_DETERMINISTIC = 1u << 1,
+  /* Adjoint only: do NOT zero-fill `grad` first (the reference always returns a
+   * fresh grid, src/tracer.cpp:401-403; set this to accumulate several ray
+   * batches into one grid). */
+  DRRT_ACCUMULATE = 1u << 2
+};
+
+int drrt_abi_version(void);
+const char *drrt_last_error(void);
+/* Number of kernels launched by this library in this process so far. */
+int64_t drrt_launch_count(void);
+
+/* ---- forward traces -------------------------------------------------------
+ * drrt_trace        <- TracerC.trace        (src/drrt.cpp:51, src/tracer.cpp:35-100)
+ * drrt_trace_plane  <- TracerC.trace_pln    (src/drrt.cpp:52, src/tracer.cpp:102-172)
+ * drrt_trace_target <- TracerC.trace_target (src/drrt.cpp:54, src/tracer.cpp:174-242)
+ * drrt_trace_sdf    <- TracerC.trace_sdf    (src/drrt.cpp:53, src/tracer.cpp:244-310)
+ * drrt_trace_cable  <- TracerC.trace_cable  (src/drrt.cpp:55, src/tracer.cpp:312-382)
+ */
+int drrt_trace(const float *rif, int W, int H, int D, const float *pos, const float *vel,
+               int64_t N, int layout, float h, float ds, float *xt, float *vt, int64_t *stats,
+               unsigned flags, drrt_stream_t stream);
+
+int drrt_trace_plane(const float *rif, int W, int H, int D, const float *pos, const float *vel,
+                     const float *pln_o, const float *pln_d, int64_t N, int layout, float h,
+                     float ds, float *xt, float *vt, uint8_t *not_escaped, int64_t *stats,
+                     unsigned flags, drrt_stream_t stream);
+
+int drrt_trace_target(const float *rif, int W, int H, int D, const float *pos, const float *vel,
+                      const float *target, int64_t N, int layout, float h, float ds, float *xt,
+                      float *vt, float *dist2, int64_t *stats, unsigned flags,
+                      drrt_stream_t stream);
+
+int drrt_trace_sdf(const float *rif, const float *sdf, int W, int H, int D, const float *pos,
+                   const float *vel, int64_t N, int layout, float h, float ds, float *xt,
+                   float *vt, int64_t *stats, unsigned flags, drrt_stream_t stream);
+
+int drrt_trace_cable(const float *rif, int res, float radius, float length, const float *pos,
+                     const float *vel, const float *target, int64_t N, int layout, float ds,
+                     float *xt, float *vt, float *dist2, int64_t *stats, unsigned flags,
+                     drrt_stream_t stream);
+
+/* ---- adjoints -------------------------------------------------------------
+ * drrt_backtrace       <- TracerC.backtrace       (src/drrt.cpp:56, src/tracer.cpp:384-440)
+ * drrt_backtrace_sdf   <- TracerC.backtrace_sdf   (src/drrt.cpp:57, src/tracer.cpp:443-509)
+ * drrt_backtrace_cable <- TracerC.backtrace_cable (src/drrt.cpp:58, src/tracer.cpp:511-567)
+ * `grad` has W*H*D (resp. `res`) floats.  DRRT_DETERMINISTIC needs `scratch`:
+ * a device buffer of drrt_backtrace_scratch_bytes(...) bytes (NULL otherwise).
+ */
+size_t drrt_backtrace_scratch_bytes(int64_t grid_elems, unsigned flags);
+
+int drrt_backtrace(const float *rif, int W, int H, int D, const float *xt, const float *vt,
+                   const float *dx, const float *dv, int64_t N, int layout, float h, float ds,
+                   float *grad, void *scratch, int64_t *stats, unsigned flags,
+                   drrt_stream_t stream);
+
+int drrt_backtrace_sdf(const float *rif, const float *sdf, int W, int H, int D, const float *xt,
+                       const float *vt, const float *dx, const float *dv, int64_t N, int layout,
+                       float h, float ds, float *grad, void *scratch, int64_t *stats,
+                       unsigned flags, drrt_stream_t stream);
+
+int drrt_backtrace_cable(const float *rif, int res, float radius, float length, const float *xt,
+                         const float *vt, const float *dx, const float *dv, int64_t N, int layout,
+                         float ds, float *grad, void *scratch, int64_t *stats, unsigned flags,
+                         drrt_stream_t stream);
+
+/* ---- volume primitives (parity probes; reference src/test.cpp:61-101) -------
+ * drrt_volume_eval   <- volume::eval_grad + eval_hess (src/volume.cpp:101-181, :40-99)
+ *                       hess = (N,3): d2/dxdy, d2/dxdz, d2/dydz
+ * drrt_volume_splat  <- volume::splat (src/volume.cpp:182-244), accumulates into `data`
+ * drrt_cylinder_eval <- cylinder_volume::eval_grad + eval_hess
+ *                       (src/cylinder_volume.cpp:26-111), hess = (N,9) row-major
+ * drrt_cylinder_splat<- cylinder_volume::splat (src/cylinder_volume.cpp:113-148)
+ */
+int drrt_volume_eval(const float *rif, int W, int H, int D, const float *pos, int64_t N,
+                     int layout, float h, float *n, float *grad, float *hess, unsigned flags,
+                     drrt_stream_t stream);
+int drrt_volume_splat(float *data, int W, int H, int D, const float *pos, const float *val,
+                      const float *grad, int64_t N, int layout, float h, drrt_stream_t stream);
+int drrt_cylinder_eval(const float *rif, int res, float radius, float length, const float *pos,
+                       int64_t N, int layout, float *n, float *grad, float *hess,
+                       drrt_stream_t stream);
+int drrt_cylinder_splat(float *data, int res, float radius, float length, const float *pos,
+                        const float *val, const float *grad, int64_t N, int layout,
+                        drrt_stream_t stream);
+
+/* ---- host-buffer entry points (what a non-torch binding of the reference API
+ * calls; device memory is managed inside the library and cached per thread) --- */
+int drrt_trace_host(const float *rif, int W, int H, int D, const float *pos, const float *vel,
+                    int64_t N, int layout, float h, float ds, float *xt, float *vt,
+                    int64_t *stats, unsigned flags);
+int drrt_backtrace_host(const float *rif, int W, int H, int D, const float *xt, const float *vt,
+                        const float *dx, const float *dv, int64_t N, int layout, float h,
+                        float ds, float *grad, int64_t *stats, unsigned flags);
+/* Keep `rif` resident on the device between _host calls of this thread: when
+ * enabled, the grid is uploaded only if its host pointer or dimensions differ
+ * from the previous call, or after drrt_host_invalidate_grid().  Default: off
+ * (upload on every call). */
+void drrt_host_cache_grid(int enable);
+void drrt_host_invalidate_grid(void);
+/* Free this thread's cached device buffers and stream. */
+void drrt_host_release(void);
+
+/* ---- multi-GPU: one private gradient grid per rank, summed over NVLink ------
+ * The communicator is an ncclComm_t created by the caller or by
+ * drrt_comm_init_rank() from an id all ranks share. */
+#define DRRT_UNIQUE_ID_BYTES 128
+int drrt_comm_unique_id(char id[DRRT_UNIQUE_ID_BYTES]);
+int drrt_comm_init_rank(void **comm, int nranks, const char id[DRRT_UNIQUE_ID_BYTES], int rank);
+int drrt_comm_destroy(void *comm);
+int drrt_allreduce_grad(float *grad, size_t count, void *comm, drrt_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DRRT_B200_H */
