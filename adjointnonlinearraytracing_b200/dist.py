@@ -1,0 +1,107 @@
+"""Multi-GPU path: rays shard across ranks, each rank accumulates a private
+gradient grid, the grids are summed with ONE all-reduce over NVLink
+(SURVEY.md section 8e).  One process per GPU; ``torch.distributed`` supplies
+rendezvous only -- the collective itself is ``drrt_allreduce_grad`` on a NCCL
+communicator this library creates (``drrt_comm_init_rank``), enqueued on the same
+stream as the adjoint kernel so no host synchronisation separates them.
+
+The reference is single-GPU (no collective anywhere in it); this module is new.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_void_p
+from typing import Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from . import _capi, ops
+
+
+def shard_bounds(n: int, rank: int, world: int) -> Tuple[int, int]:
+    """Contiguous, balanced [start, end) block of `n` rays for `rank` (earlier ranks take the
+    remainder).  Contiguous blocks keep whole sensor rows/views together, which keeps a warp's
+    rays spatially coherent."""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError("bad rank/world")
+    base, rem = divmod(n, world)
+    start = rank * base + min(rank, rem)
+    return start, start + base + (1 if rank < rem else 0)
+
+
+def shard_rays(rank: int, world: int, *tensors):
+    """Slice every (N, 3) / (N,) tensor to this rank's block."""
+    n = tensors[0].shape[0]
+    a, b = shard_bounds(n, rank, world)
+    return tuple(t[a:b].contiguous() for t in tensors)
+
+
+class GradAllReduce:
+    """Sum-all-reduce of the private gradient grids.
+
+    backend="nccl-native": a NCCL communicator owned by libdrrt_b200.so; the unique id is
+    broadcast through the existing torch.distributed group.  backend="torch": plain
+    ``torch.distributed.all_reduce`` (used by the gloo CPU tests of the host logic).
+    """
+
+    def __init__(self, backend: Optional[str] = None, group=None):
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        if backend is None:
+            backend = "nccl-native" if (self.world > 1 and dist.get_backend(group) == "nccl") else "torch"
+        self.backend = backend
+        self.comm = None
+        if self.world > 1 and backend == "nccl-native":
+            lib = _capi.load()
+            buf = ctypes.create_string_buffer(_capi.DRRT_UNIQUE_ID_BYTES)
+            if self.rank == 0:
+                _capi.check(lib.drrt_comm_unique_id(buf))
+            box = [bytes(buf.raw)]
+            dist.broadcast_object_list(box, src=0, group=group)
+            uid = ctypes.create_string_buffer(box[0], _capi.DRRT_UNIQUE_ID_BYTES)
+            comm = c_void_p()
+            _capi.check(lib.drrt_comm_init_rank(ctypes.byref(comm), self.world, uid, self.rank))
+            self.comm = comm
+
+    def __call__(self, grad: torch.Tensor) -> torch.Tensor:
+        if self.world == 1:
+            return grad
+        if self.backend == "nccl-native":
+            if not grad.is_cuda or not grad.is_contiguous() or grad.dtype != torch.float32:
+                raise RuntimeError("grad must be a contiguous float32 CUDA tensor")
+            stream = c_void_p(torch.cuda.current_stream(grad.device).cuda_stream)
+            _capi.check(_capi.load().drrt_allreduce_grad(c_void_p(grad.data_ptr()), grad.numel(), self.comm, stream))
+        else:
+            dist.all_reduce(grad, op=dist.ReduceOp.SUM, group=self.group)
+        return grad
+
+    def close(self):
+        if self.comm is not None:
+            _capi.load().drrt_comm_destroy(self.comm)
+            self.comm = None
+
+
+class ShardedTracer:
+    """Forward + adjoint over this rank's ray block with the all-reduced gradient.
+
+    >>> st = ShardedTracer(rif, h, ds)            # rif replicated on every rank
+    >>> xt, vt = st.trace(pos_local, vel_local)   # outputs stay sharded (per-ray loss)
+    >>> grad = st.backtrace(xt, vt, dx, dv)       # identical on every rank after the sum
+    """
+
+    def __init__(self, rif: torch.Tensor, h: float, ds: float, flags: int = 0,
+                 allreduce: Optional[GradAllReduce] = None):
+        self.rif, self.h, self.ds, self.flags = rif, float(h), float(ds), int(flags)
+        self.allreduce = allreduce if allreduce is not None else GradAllReduce()
+        self.grad = torch.empty_like(rif)
+        self.stats = ops.new_stats(rif.device) if rif.is_cuda else None
+
+    def trace(self, pos, vel):
+        return ops.trace(self.rif, pos, vel, self.h, self.ds, flags=self.flags, stats=self.stats)
+
+    def backtrace(self, xt, vt, dx, dv):
+        g = ops.backtrace(self.rif, xt, vt, dx, dv, self.h, self.ds, flags=self.flags, stats=self.stats,
+                          out=self.grad)
+        return self.allreduce(g)
