@@ -19,6 +19,6 @@ timeout 300 $CMD > $OUT/plain2_$TAG.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:backtrace_kernel -s 3 -c 1 -f -o $OUT/prof_adj_$TAG $CMD > $OUT/ncu_full_adj_$TAG.log 2>&1
 echo "ncu full adj rc=$?"
 timeout 300 $CMD > $OUT/plain3_$TAG.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:trace_kernel -s 3 -c 1 -f -o $OUT/prof_fwd_$TAG $CMD > $OUT/ncu_full_fwd_$TAG.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:^trace_kernel -s 3 -c 1 -f -o $OUT/prof_fwd_$TAG $CMD > $OUT/ncu_full_fwd_$TAG.log 2>&1
 echo "ncu full fwd rc=$?"
 ls -la $OUT | tail -20
