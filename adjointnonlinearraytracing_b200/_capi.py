@@ -17,6 +17,8 @@ DRRT_SOA, DRRT_AOS = 1, 3
 DRRT_REFERENCE_ARITH = 1 << 0
 DRRT_DETERMINISTIC = 1 << 1
 DRRT_ACCUMULATE = 1 << 2
+DRRT_FAST_ARITH = 1 << 3
+DRRT_NO_WARP_AGGREGATION = 1 << 4
 DRRT_UNIQUE_ID_BYTES = 128
 
 # every symbol include/drrt_b200.h declares (checked by tests/test_capi_symbols.py)

@@ -95,7 +95,14 @@ int check_rays(int64_t N, int layout, float ds) {
   return DRRT_OK;
 }
 
-constexpr size_t kFixedTail = 16;  // max_bits word, padded
+constexpr size_t kFixedTail = 16;
+
+// 0 fast polynomial, 1 reference-literal, 2 exact-trajectory (default)
+int arith_of(unsigned flags) {
+  if (flags & DRRT_REFERENCE_ARITH) return 1;
+  if (flags & DRRT_FAST_ARITH) return 0;
+  return 2;
+}  // max_bits word, padded
 
 int trace_common(int kind, const float *rif, const float *sdf, int W, int H, int D,
                  const float *pos, const float *vel, const float *aux0, const float *aux1,
@@ -124,7 +131,7 @@ int trace_common(int kind, const float *rif, const float *sdf, int W, int H, int
     a.tail_max_iters = a.tail_iters + N;
     CU_TRY(cudaMemsetAsync(a.tail_max_iters, 0, sizeof(int), s));
   }
-  g_launches += launch_trace(kind, (flags & DRRT_REFERENCE_ARITH) != 0, a, s);
+  g_launches += launch_trace(kind, arith_of(flags), a, s);
   rc = check_launch("trace");
   if (tail) cudaFreeAsync(tail, s);
   return rc;
@@ -158,7 +165,7 @@ int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, i
     CU_TRY(cudaMemsetAsync(scratch, 0, sizeof(unsigned long long) * (size_t) G + kFixedTail, s));
     g_launches += launch_fixed_max(dx, dv, 3 * N, max_bits, s);
   }
-  g_launches += launch_backtrace(sdf_kind, (flags & DRRT_REFERENCE_ARITH) != 0, a, grad, fixed, max_bits, s);
+  g_launches += launch_backtrace(sdf_kind, arith_of(flags), !(flags & DRRT_NO_WARP_AGGREGATION), a, grad, fixed, max_bits, s);
   if (det) g_launches += launch_fixed_to_float(fixed, max_bits, grad, G, accumulate, s);
   return check_launch("backtrace");
 }
@@ -286,7 +293,7 @@ int drrt_volume_eval(const float *rif, int W, int H, int D, const float *pos, in
   int rc = make_grid(g, rif, W, H, D, h);
   if (rc) return rc;
   if ((rc = check_rays(N, layout, 1.0f))) return rc;
-  g_launches += launch_volume_eval(g, pos, N, layout, n, grad, hess, (flags & DRRT_REFERENCE_ARITH) != 0,
+  g_launches += launch_volume_eval(g, pos, N, layout, n, grad, hess, !(flags & DRRT_FAST_ARITH),
                                    (cudaStream_t) stream);
   return check_launch("volume_eval");
 }

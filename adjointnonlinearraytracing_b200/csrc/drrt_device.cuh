@@ -102,6 +102,32 @@ __device__ __forceinline__ void corner_indices(const GridP &g, int cx, int cy, i
   idx[4] = r01 + x0; idx[5] = r01 + x1; idx[6] = r11 + x0; idx[7] = r11 + x1;
 }
 
+// Compact form of the same 8 addresses: base = idx[0] and the three (clamped)
+// strides, idx[k] = base + (k&1 ? dx : 0) + (k&2 ? dy : 0) + (k&4 ? dz : 0).
+struct CellAddr {
+  int base, dx, dy, dz;
+  __device__ __forceinline__ int at(int k) const {
+    return base + ((k & 1) ? dx : 0) + ((k & 2) ? dy : 0) + ((k & 4) ? dz : 0);
+  }
+};
+
+__device__ __forceinline__ CellAddr corner_addr(const GridP &g, int cx, int cy, int cz) {
+  int x0 = max(min(cx, g.W - 1), 0), x1 = max(min(cx + 1, g.W - 1), 0);
+  int y0 = max(min(cy, g.H - 1), 0), y1 = max(min(cy + 1, g.H - 1), 0);
+  int z0 = max(min(cz, g.D - 1), 0), z1 = max(min(cz + 1, g.D - 1), 0);
+  CellAddr a;
+  a.base = (z0 * g.H + y0) * g.W + x0;
+  a.dx = x1 - x0;
+  a.dy = (y1 - y0) * g.W;
+  a.dz = (z1 - z0) * g.H * g.W;
+  return a;
+}
+
+__device__ __forceinline__ void load_corners(const GridP &g, const CellAddr &a, float v[8]) {
+#pragma unroll
+  for (int k = 0; k < 8; ++k) v[k] = __ldg(g.data + a.at(k));
+}
+
 __device__ __forceinline__ void load_corners(const GridP &g, const int idx[8], float v[8]) {
 #pragma unroll
   for (int k = 0; k < 8; ++k) v[k] = __ldg(g.data + idx[k]);

@@ -17,16 +17,25 @@ namespace drrt {
 
 enum { K_PLAIN = 0, K_PLANE = 1, K_TARGET = 2, K_SDF = 3 };
 
-// Register cache of the cell a ray is in.  REF keeps the 8 corner values,
-// otherwise the 8 polynomial coefficients.
-template <bool REF>
+// Arithmetic flavours (see drrt_device.cuh and DESIGN.md section 4):
+//   A_FAST    factored per-cell polynomial everywhere
+//   A_REF     the reference's literal operation order everywhere
+//   A_EXACT   (default) the ray trajectory -- cell lookup, n, grad n, the v and x
+//             updates, every branch -- in the reference's literal operation order,
+//             so endpoints and the set of visited cells are bit-identical to A_REF;
+//             the quantities that only feed the (linear) gradient accumulation --
+//             Hessian, splat weights, lambda/mu -- in factored FMA form.
+enum { A_FAST = 0, A_REF = 1, A_EXACT = 2 };
+
+// Register cache of the cell a ray is in.
+template <int AR>
 struct CellCache;
 
 template <>
-struct CellCache<true> {
+struct CellCache<A_REF> {
   int cx = INT_MIN, cy = 0, cz = 0;
   float v[8];
-  __device__ __forceinline__ void refill(const GridP &g, const int idx[8]) { load_corners(g, idx, v); }
+  __device__ __forceinline__ void refill(const GridP &g, const CellAddr &a) { load_corners(g, a, v); }
   __device__ __forceinline__ void eval(const GridP &g, const CellIdx &c, float &n, f3 &nx, f3 *hm) const {
     eval_grad_ref(g, v, c.wx, c.wy, c.wz, n, nx);
     if (hm) *hm = eval_hess_ref(g, v, c.wx, c.wy, c.wz);
@@ -34,12 +43,12 @@ struct CellCache<true> {
 };
 
 template <>
-struct CellCache<false> {
+struct CellCache<A_FAST> {
   int cx = INT_MIN, cy = 0, cz = 0;
   CellPoly p;
-  __device__ __forceinline__ void refill(const GridP &g, const int idx[8]) {
+  __device__ __forceinline__ void refill(const GridP &g, const CellAddr &a) {
     float v[8];
-    load_corners(g, idx, v);
+    load_corners(g, a, v);
     p = make_poly(v);
   }
   // nx and hm are returned in world units
@@ -54,19 +63,48 @@ struct CellCache<false> {
   }
 };
 
-template <bool REF>
-__device__ __forceinline__ bool cell_changed(const CellCache<REF> &cc, const CellIdx &c) {
+template <>
+struct CellCache<A_EXACT> {
+  int cx = INT_MIN, cy = 0, cz = 0;
+  float v[8];
+  // mixed second differences in the reference's association order
+  // (src/volume.cpp:79-90; they cancel to ~1e-4 of the voxel values, so the order
+  // of the subtractions matters at the 1e-3 relative level), pre-scaled by 1/h^2:
+  // d?0 at w = 0 and the slope d?1 - d?0.
+  float hxy0, hxys, hxz0, hxzs, hyz0, hyzs;
+  __device__ __forceinline__ void refill(const GridP &g, const CellAddr &a) {
+    load_corners(g, a, v);
+    const float r2 = mul_(g.rcp_h, g.rcp_h);
+    const float v000 = v[0], v100 = v[1], v010 = v[2], v110 = v[3];
+    const float v001 = v[4], v101 = v[5], v011 = v[6], v111 = v[7];
+    float a0 = add_(sub_(sub_(v110, v010), v100), v000), a1 = add_(sub_(sub_(v111, v011), v101), v001);
+    float b0 = add_(sub_(sub_(v101, v001), v100), v000), b1 = add_(sub_(sub_(v111, v011), v110), v010);
+    float c0 = add_(sub_(sub_(v011, v001), v010), v000), c1 = add_(sub_(sub_(v111, v101), v110), v100);
+    hxy0 = a0 * r2; hxys = (a1 - a0) * r2;
+    hxz0 = b0 * r2; hxzs = (b1 - b0) * r2;
+    hyz0 = c0 * r2; hyzs = (c1 - c0) * r2;
+  }
+  __device__ __forceinline__ void eval(const GridP &g, const CellIdx &c, float &n, f3 &nx, f3 *hm) const {
+    eval_grad_ref(g, v, c.wx, c.wy, c.wz, n, nx);
+    if (hm) {
+      hm->x = fmaf(hxys, c.wz, hxy0);
+      hm->y = fmaf(hxzs, c.wy, hxz0);
+      hm->z = fmaf(hyzs, c.wx, hyz0);
+    }
+  }
+};
+
+template <int AR>
+__device__ __forceinline__ bool cell_changed(const CellCache<AR> &cc, const CellIdx &c) {
   return (c.cx != cc.cx) | (c.cy != cc.cy) | (c.cz != cc.cz);
 }
 
 // Trilinear value only (sdf lookups), src/volume.cpp:162-163 under the caller's mask.
-template <bool REF>
-__device__ __forceinline__ float eval_value(const GridP &g, CellCache<REF> &cc, f3 x) {
+template <int AR>
+__device__ __forceinline__ float eval_value(const GridP &g, CellCache<AR> &cc, f3 x) {
   CellIdx c = cell_of(g, x);
   if (cell_changed(cc, c)) {
-    int idx[8];
-    corner_indices(g, c.cx, c.cy, c.cz, idx);
-    cc.refill(g, idx);
+    cc.refill(g, corner_addr(g, c.cx, c.cy, c.cz));
     cc.cx = c.cx; cc.cy = c.cy; cc.cz = c.cz;
   }
   float n; f3 nx;
@@ -83,8 +121,9 @@ __device__ __forceinline__ float dist2_ref(f3 x, f3 t) {
 // Forward: Tracer::trace (src/tracer.cpp:35-100), trace_plane (:102-172),
 // trace_target (:174-242, per-ray part), trace_sdf (:244-310).
 // ---------------------------------------------------------------------------
-template <int KIND, bool REF>
+template <int KIND, int AR>
 __global__ void __launch_bounds__(kTraceThreads) trace_kernel(TraceArgs a) {
+  constexpr bool REF = AR != A_FAST;
   const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
   const bool valid = r < a.N;
   int64_t steps = 0;
@@ -100,8 +139,8 @@ __global__ void __launch_bounds__(kTraceThreads) trace_kernel(TraceArgs a) {
     if (KIND == K_TARGET) { aux0 = ld3(a.aux0, r, a.N, a.layout); best = dist2_ref(x, aux0); }
     bool inside = inbounds(g, x);  // :61
     bool esc = false;
-    CellCache<REF> cc;
-    CellCache<REF> sc;  // sdf grid (K_SDF only)
+    CellCache<AR> cc;
+    CellCache<AR> sc;  // sdf grid (K_SDF only)
     GridP sg = g;
     sg.data = a.sdf;
     int i = 0;
@@ -109,9 +148,7 @@ __global__ void __launch_bounds__(kTraceThreads) trace_kernel(TraceArgs a) {
       if (inside) {  // masked gather: outside lanes see n = 0, grad n = 0 and fly straight
         CellIdx c = cell_of(g, x);
         if (cell_changed(cc, c)) {
-          int idx[8];
-          corner_indices(g, c.cx, c.cy, c.cz, idx);
-          cc.refill(g, idx);
+          cc.refill(g, corner_addr(g, c.cx, c.cy, c.cz));
           cc.cx = c.cx; cc.cy = c.cy; cc.cz = c.cz;
         }
         float n; f3 nx;
@@ -130,7 +167,7 @@ __global__ void __launch_bounds__(kTraceThreads) trace_kernel(TraceArgs a) {
         cur_inside = inb & !(dd > 0.f);
       }
       if (KIND == K_SDF) {  // :287-288, evaluated under the previous `inside`
-        cur_inside = inside ? (eval_value<REF>(sg, sc, x) < 0.f) : false;
+        cur_inside = inside ? (eval_value<AR>(sg, sc, x) < 0.f) : false;
       }
       const bool cross = inside & !cur_inside;  // :74
       if (KIND == K_TARGET) {  // :216-227
@@ -204,109 +241,177 @@ __global__ void __launch_bounds__(kTraceThreads) trace_target_tail_kernel(TraceA
 // Adjoint: Tracer::backtrace (src/tracer.cpp:384-440), backtrace_sdf (:443-509).
 // The ray is re-integrated backwards from its stored exit state; no tape.
 //
-// Gradient splat.  REF: the reference's 16 terms, one atomic each
-// (src/volume.cpp:217-243).  Otherwise: the two terms per corner are fused
-// (8 values), and those 8 values are ACCUMULATED IN REGISTERS for as long as
-// the ray stays in the same cell; they are flushed with 8 atomics only when the
-// ray moves to another cell (ds = h/2 gives ~2 steps per cell, so ~4 atomics per
-// step instead of 16).
+// Gradient splat.
+//   A_REF: the reference's 16 terms, one atomic each (src/volume.cpp:217-243).
+//   A_EXACT / A_FAST: the two terms per corner are fused (8 values) and those 8
+//   values are ACCUMULATED IN REGISTERS while the ray stays in one cell; they are
+//   flushed when it moves on (ds = h/2: ~2 steps per cell).  With AGG the flush is
+//   warp-aggregated: lanes that flush the same cell in the same step (neighbouring
+//   sensor pixels share cells -- 8 rays per cell in the 2048^2 / 256^3 workload)
+//   are summed with a segmented shuffle reduction and one lane per run issues the
+//   8 RED.ADD.F32, so same-address conflicts inside a warp (which the LSU
+//   serialises into one L2 sector operation per lane, profiles/r01_adj_full.txt:
+//   9.7 sectors per RED request) disappear.
 // ---------------------------------------------------------------------------
-template <bool SDF, bool REF, class Accum>
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int kAggRun = 8;   // maximum run length (aligned), log2 shuffle rounds
+constexpr int kAggMin = 4;   // fewer flushing lanes than this: plain atomics
+
+template <class Accum>
+__device__ __forceinline__ void flush_direct(const Accum &out, const CellAddr &ca, float acc[8]) {
+#pragma unroll
+  for (int k = 0; k < 8; ++k) out.add(ca.at(k), acc[k]);
+}
+
+// Warp-uniform: every lane of the warp calls this with its own `fl`.
+template <class Accum>
+__device__ __forceinline__ void flush_aggregated(const Accum &out, const CellAddr &ca, float acc[8],
+                                                 bool fl, unsigned lane) {
+  const unsigned fm = __ballot_sync(kFull, fl);
+  if (fm == 0) return;
+  if (__popc(fm) < kAggMin) {
+    if (fl) flush_direct(out, ca, acc);
+    return;
+  }
+  // two lanes address the same 8 voxels iff corner 0 and corner 7 coincide
+  const int k0 = fl ? ca.base : -1;
+  const int k7 = ca.base + ca.dx + ca.dy + ca.dz;
+  const int p0 = __shfl_up_sync(kFull, k0, 1), p7 = __shfl_up_sync(kFull, k7, 1);
+  const bool head = fl && ((lane & (kAggRun - 1)) == 0 || p0 != k0 || p7 != k7);
+  const unsigned stops = __ballot_sync(kFull, head || !fl);
+  const unsigned above = stops & ~((2u << lane) - 1u);
+  const int end = above ? __ffs(above) - 1 : 32;
+#pragma unroll
+  for (int off = 1; off < kAggRun; off <<= 1) {
+    const bool take = (int) (lane + off) < end;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float t = __shfl_down_sync(kFull, acc[k], off);
+      if (take) acc[k] += t;
+    }
+  }
+  if (head) flush_direct(out, ca, acc);
+}
+
+template <bool SDF, int AR, class Accum, bool AGG>
 __global__ void __launch_bounds__(kAdjThreads) backtrace_kernel(AdjArgs a, Accum out_in) {
+  constexpr bool REF = AR == A_REF;     // literal 16-atomic splat and lambda/mu order
+  constexpr bool TRAJ_REF = AR != A_FAST;
   Accum out = out_in;
   out.prepare();
   const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned lane = threadIdx.x & 31;
   const bool valid = r < a.N;
   int64_t steps = 0;
+  const GridP g = a.grid;
+  const float ds = a.ds;
+  f3 x = {0, 0, 0}, v = {0, 0, 0}, la = {0, 0, 0}, mu = {0, 0, 0};
+  bool active = false;
+  CellCache<AR> cc;
+  CellCache<AR> sc;
+  GridP sg = g;
+  sg.data = a.sdf;
+  bool outside = false;
   if (valid) {
-    const GridP g = a.grid;
-    const float ds = a.ds;
-    f3 x = ld3(a.xt, r, a.N, a.layout), v = ld3(a.vt, r, a.N, a.layout);
-    f3 la = ld3(a.dx, r, a.N, a.layout), mu = ld3(a.dv, r, a.N, a.layout);
+    x = ld3(a.xt, r, a.N, a.layout); v = ld3(a.vt, r, a.N, a.layout);
+    la = ld3(a.dx, r, a.N, a.layout); mu = ld3(a.dv, r, a.N, a.layout);
     mu.x = add_(mu.x, mul_(ds, la.x)); mu.y = add_(mu.y, mul_(ds, la.y)); mu.z = add_(mu.z, mul_(ds, la.z));  // :410
     f3 nv = {-v.x, -v.y, -v.z};
-    bool active = !escaped(g, x, nv);  // :413-414
-    CellCache<REF> cc;
-    CellCache<REF> sc;
-    GridP sg = g;
-    sg.data = a.sdf;
-    bool outside = false;
+    active = !escaped(g, x, nv);  // :413-414
     if (SDF) {  // :476-477
-      float dist = active ? eval_value<REF>(sg, sc, x) : 0.f;
+      float dist = active ? eval_value<AR>(sg, sc, x) : 0.f;
       outside = dist >= 0.f;
     }
-    int idx[8];
-    float acc[8];
+  }
+  CellAddr ca = {0, 0, 0, 0};
+  float acc[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) { acc[k] = 0.f; idx[k] = 0; }
-    bool have = false;
-    for (int i = 0; active && i < a.max_steps; ++i) {
+  for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+  bool have = false;
+  for (int i = 0; i < a.max_steps; ++i) {
+    if (AGG) {
+      if (!__any_sync(kFull, active)) break;
+    } else if (!active) {
+      break;
+    }
+    CellIdx c = {0, 0, 0, 0.f, 0.f, 0.f};
+    bool chg = false;
+    if (active) {
       x.x = fmaf(-ds, v.x, x.x); x.y = fmaf(-ds, v.y, x.y); x.z = fmaf(-ds, v.z, x.z);  // :420
-      CellIdx c = cell_of(g, x);
-      if (cell_changed(cc, c)) {
-        if (!REF && have) {
+      c = cell_of(g, x);
+      chg = cell_changed(cc, c);
+    }
+    if (!REF) {
+      const bool fl = have && (chg || !active);
+      if (AGG) flush_aggregated(out, ca, acc, fl, lane);
+      else if (fl) flush_direct(out, ca, acc);
+      if (fl) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k) { out.add(idx[k], acc[k]); acc[k] = 0.f; }
-          have = false;
-        }
-        corner_indices(g, c.cx, c.cy, c.cz, idx);
-        cc.refill(g, idx);
+        for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+        have = false;
+      }
+    }
+    if (active) {
+      if (chg) {
+        ca = corner_addr(g, c.cx, c.cy, c.cz);
+        cc.refill(g, ca);
         cc.cx = c.cx; cc.cy = c.cy; cc.cz = c.cz;
       }
       float n; f3 nx, hm;
       cc.eval(g, c, n, nx, &hm);  // :421-422 (same 8 voxels serve grad and Hessian)
-      float mdsn = REF ? mul_(-ds, n) : -ds * n;
+      float mdsn = TRAJ_REF ? mul_(-ds, n) : -ds * n;
       v.x = fmaf(mdsn, nx.x, v.x); v.y = fmaf(mdsn, nx.y, v.y); v.z = fmaf(mdsn, nx.z, v.z);  // :423
       ++steps;
-      nv.x = -v.x; nv.y = -v.y; nv.z = -v.z;
+      f3 nv = {-v.x, -v.y, -v.z};
       active = inbounds(g, x) || !escaped(g, x, nv);  // :425
       if (SDF) {  // :488-497
-        float dist = eval_value<REF>(sg, sc, x);
+        float dist = eval_value<AR>(sg, sc, x);
         bool now_out = dist >= 0.f;
         active = active & !(!outside & now_out);
         outside = now_out;
       }
-      if (!active) break;  // :426 per ray
-      if (REF) {
-        float dn = fma_(mu.z, nx.z, fma_(mu.y, nx.y, mul_(mu.x, nx.x)));  // :430
-        f3 dnx = {mul_(mul_(n, mu.x), ds), mul_(mul_(n, mu.y), ds), mul_(mul_(n, mu.z), ds)};  // :431-432
-        float t[16];
-        splat_terms_ref(mul_(dn, ds), dnx, c.wx, c.wy, c.wz, t);
+      if (active) {  // :426 per ray
+        if (REF) {
+          float dn = fma_(mu.z, nx.z, fma_(mu.y, nx.y, mul_(mu.x, nx.x)));  // :430
+          f3 dnx = {mul_(mul_(n, mu.x), ds), mul_(mul_(n, mu.y), ds), mul_(mul_(n, mu.z), ds)};  // :431-432
+          float t[16];
+          splat_terms_ref(mul_(dn, ds), dnx, c.wx, c.wy, c.wz, t);
 #pragma unroll
-        for (int k = 0; k < 16; ++k) out.add(idx[k & 7], t[k]);
-        // :434  la += ds * (dn * nx + (n * Hess) * mu), matrix.h:170-178 column sums
-        float nhxy = mul_(n, hm.x), nhxz = mul_(n, hm.y), nhyz = mul_(n, hm.z);
-        float h0 = fma_(nhxz, mu.z, mul_(nhxy, mu.y));
-        float h1 = fma_(nhyz, mu.z, mul_(nhxy, mu.x));
-        float h2 = fma_(nhyz, mu.y, mul_(nhxz, mu.x));
-        la.x = add_(la.x, mul_(ds, add_(mul_(dn, nx.x), h0)));
-        la.y = add_(la.y, mul_(ds, add_(mul_(dn, nx.y), h1)));
-        la.z = add_(la.z, mul_(ds, add_(mul_(dn, nx.z), h2)));
-        mu.x = add_(mu.x, mul_(ds, la.x)); mu.y = add_(mu.y, mul_(ds, la.y)); mu.z = add_(mu.z, mul_(ds, la.z));  // :435
-      } else {
-        float dn = fmaf(mu.z, nx.z, fmaf(mu.y, nx.y, mu.x * nx.x));
-        float nds = n * ds;
-        f3 dnx = {nds * mu.x, nds * mu.y, nds * mu.z};
-        splat_accumulate(dn * ds, dnx, c.wx, c.wy, c.wz, acc);
-        have = true;
-        float nhxy = n * hm.x, nhxz = n * hm.y, nhyz = n * hm.z;
-        float h0 = fmaf(nhxz, mu.z, nhxy * mu.y);
-        float h1 = fmaf(nhyz, mu.z, nhxy * mu.x);
-        float h2 = fmaf(nhyz, mu.y, nhxz * mu.x);
-        la.x = fmaf(ds, fmaf(dn, nx.x, h0), la.x);
-        la.y = fmaf(ds, fmaf(dn, nx.y, h1), la.y);
-        la.z = fmaf(ds, fmaf(dn, nx.z, h2), la.z);
-        mu.x = fmaf(ds, la.x, mu.x); mu.y = fmaf(ds, la.y, mu.y); mu.z = fmaf(ds, la.z, mu.z);
+          for (int k = 0; k < 16; ++k) out.add(ca.at(k & 7), t[k]);
+          // :434  la += ds * (dn * nx + (n * Hess) * mu), matrix.h:170-178 column sums
+          float nhxy = mul_(n, hm.x), nhxz = mul_(n, hm.y), nhyz = mul_(n, hm.z);
+          float h0 = fma_(nhxz, mu.z, mul_(nhxy, mu.y));
+          float h1 = fma_(nhyz, mu.z, mul_(nhxy, mu.x));
+          float h2 = fma_(nhyz, mu.y, mul_(nhxz, mu.x));
+          la.x = add_(la.x, mul_(ds, add_(mul_(dn, nx.x), h0)));
+          la.y = add_(la.y, mul_(ds, add_(mul_(dn, nx.y), h1)));
+          la.z = add_(la.z, mul_(ds, add_(mul_(dn, nx.z), h2)));
+          mu.x = add_(mu.x, mul_(ds, la.x)); mu.y = add_(mu.y, mul_(ds, la.y)); mu.z = add_(mu.z, mul_(ds, la.z));  // :435
+        } else {
+          float dn = fmaf(mu.z, nx.z, fmaf(mu.y, nx.y, mu.x * nx.x));
+          float nds = n * ds;
+          f3 dnx = {nds * mu.x, nds * mu.y, nds * mu.z};
+          splat_accumulate(dn * ds, dnx, c.wx, c.wy, c.wz, acc);
+          have = true;
+          float nhxy = n * hm.x, nhxz = n * hm.y, nhyz = n * hm.z;
+          float h0 = fmaf(nhxz, mu.z, nhxy * mu.y);
+          float h1 = fmaf(nhyz, mu.z, nhxy * mu.x);
+          float h2 = fmaf(nhyz, mu.y, nhxz * mu.x);
+          la.x = fmaf(ds, fmaf(dn, nx.x, h0), la.x);
+          la.y = fmaf(ds, fmaf(dn, nx.y, h1), la.y);
+          la.z = fmaf(ds, fmaf(dn, nx.z, h2), la.z);
+          mu.x = fmaf(ds, la.x, mu.x); mu.y = fmaf(ds, la.y, mu.y); mu.z = fmaf(ds, la.z, mu.z);
+        }
       }
     }
-    if (!REF && have) {
-#pragma unroll
-      for (int k = 0; k < 8; ++k) out.add(idx[k], acc[k]);
-    }
+  }
+  if (!REF) {
+    if (AGG) flush_aggregated(out, ca, acc, have, lane);
+    else if (have) flush_direct(out, ca, acc);
   }
   if (a.stats) {
     steps = warp_sum_i64(steps);
-    if ((threadIdx.x & 31) == 0 && steps) atomicAdd((unsigned long long *) a.stats, (unsigned long long) steps);
+    if (lane == 0 && steps) atomicAdd((unsigned long long *) a.stats, (unsigned long long) steps);
   }
 }
 
@@ -316,44 +421,52 @@ __global__ void __launch_bounds__(kAdjThreads) backtrace_kernel(AdjArgs a, Accum
 static inline unsigned blocks_for(int64_t n, int threads) { return (unsigned) ((n + threads - 1) / threads); }
 
 template <int KIND>
-static void launch_trace_kind(bool ref, const TraceArgs &a, cudaStream_t s) {
+static void launch_trace_kind(int arith, const TraceArgs &a, cudaStream_t s) {
   unsigned nb = blocks_for(a.N, kTraceThreads);
-  if (ref) trace_kernel<KIND, true><<<nb, kTraceThreads, 0, s>>>(a);
-  else trace_kernel<KIND, false><<<nb, kTraceThreads, 0, s>>>(a);
+  // the forward pass is all trajectory: A_EXACT and A_REF are the same kernel
+  if (arith == A_FAST) trace_kernel<KIND, A_FAST><<<nb, kTraceThreads, 0, s>>>(a);
+  else trace_kernel<KIND, A_REF><<<nb, kTraceThreads, 0, s>>>(a);
 }
 
-int launch_trace(int kind, bool ref_arith, const TraceArgs &a, cudaStream_t s) {
+int launch_trace(int kind, int arith, const TraceArgs &a, cudaStream_t s) {
   if (a.N <= 0) return 0;
   switch (kind) {
-    case K_PLAIN: launch_trace_kind<K_PLAIN>(ref_arith, a, s); return 1;
-    case K_PLANE: launch_trace_kind<K_PLANE>(ref_arith, a, s); return 1;
-    case K_SDF: launch_trace_kind<K_SDF>(ref_arith, a, s); return 1;
+    case K_PLAIN: launch_trace_kind<K_PLAIN>(arith, a, s); return 1;
+    case K_PLANE: launch_trace_kind<K_PLANE>(arith, a, s); return 1;
+    case K_SDF: launch_trace_kind<K_SDF>(arith, a, s); return 1;
     case K_TARGET:
-      launch_trace_kind<K_TARGET>(ref_arith, a, s);
+      launch_trace_kind<K_TARGET>(arith, a, s);
       trace_target_tail_kernel<<<blocks_for(a.N, kTraceThreads), kTraceThreads, 0, s>>>(a);
       return 2;
   }
   return 0;
 }
 
-template <bool SDF, class Accum>
-static void launch_backtrace_acc(bool ref, const AdjArgs &a, Accum acc, cudaStream_t s) {
+template <bool SDF, class Accum, bool AGG>
+static void launch_backtrace_acc(int arith, const AdjArgs &a, Accum acc, cudaStream_t s) {
   unsigned nb = blocks_for(a.N, kAdjThreads);
-  if (ref) backtrace_kernel<SDF, true, Accum><<<nb, kAdjThreads, 0, s>>>(a, acc);
-  else backtrace_kernel<SDF, false, Accum><<<nb, kAdjThreads, 0, s>>>(a, acc);
+  if (arith == A_REF) backtrace_kernel<SDF, A_REF, Accum, false><<<nb, kAdjThreads, 0, s>>>(a, acc);
+  else if (arith == A_FAST) backtrace_kernel<SDF, A_FAST, Accum, AGG><<<nb, kAdjThreads, 0, s>>>(a, acc);
+  else backtrace_kernel<SDF, A_EXACT, Accum, AGG><<<nb, kAdjThreads, 0, s>>>(a, acc);
 }
 
-int launch_backtrace(bool sdf, bool ref_arith, const AdjArgs &a, float *grad,
+int launch_backtrace(bool sdf, int arith, bool warp_agg, const AdjArgs &a, float *grad,
                      unsigned long long *fixed, const unsigned *fixed_max_bits, cudaStream_t s) {
   if (a.N <= 0) return 0;
   if (fixed) {
+    // integer accumulation must not depend on how lanes are grouped: no float pre-summation
     AccumFixed acc{fixed, fixed_max_bits, 1.0f};
-    if (sdf) launch_backtrace_acc<true>(ref_arith, a, acc, s);
-    else launch_backtrace_acc<false>(ref_arith, a, acc, s);
+    if (sdf) launch_backtrace_acc<true, AccumFixed, false>(arith, a, acc, s);
+    else launch_backtrace_acc<false, AccumFixed, false>(arith, a, acc, s);
   } else {
     AccumFloat acc{grad};
-    if (sdf) launch_backtrace_acc<true>(ref_arith, a, acc, s);
-    else launch_backtrace_acc<false>(ref_arith, a, acc, s);
+    if (sdf) {
+      if (warp_agg) launch_backtrace_acc<true, AccumFloat, true>(arith, a, acc, s);
+      else launch_backtrace_acc<true, AccumFloat, false>(arith, a, acc, s);
+    } else {
+      if (warp_agg) launch_backtrace_acc<false, AccumFloat, true>(arith, a, acc, s);
+      else launch_backtrace_acc<false, AccumFloat, false>(arith, a, acc, s);
+    }
   }
   return 1;
 }

@@ -57,8 +57,9 @@ struct CableArgs {
 };
 
 // kind: 0 plain, 1 plane, 2 target, 3 sdf.  Returns the number of kernels launched.
-int launch_trace(int kind, bool ref_arith, const TraceArgs &a, cudaStream_t s);
-int launch_backtrace(bool sdf, bool ref_arith, const AdjArgs &a, float *grad,
+// arith: 0 fast polynomial, 1 reference-literal, 2 exact-trajectory (default)
+int launch_trace(int kind, int arith, const TraceArgs &a, cudaStream_t s);
+int launch_backtrace(bool sdf, int arith, bool warp_agg, const AdjArgs &a, float *grad,
                      unsigned long long *fixed, const unsigned *fixed_max_bits, cudaStream_t s);
 int launch_trace_cable(bool ref_arith, const CableArgs &a, cudaStream_t s);
 int launch_backtrace_cable(bool ref_arith, const CableArgs &a, float *grad,

@@ -18,7 +18,8 @@ from typing import Optional, Sequence, Tuple
 import torch
 
 from . import _capi
-from ._capi import DRRT_ACCUMULATE, DRRT_AOS, DRRT_DETERMINISTIC, DRRT_REFERENCE_ARITH, DRRT_SOA
+from ._capi import (DRRT_ACCUMULATE, DRRT_AOS, DRRT_DETERMINISTIC, DRRT_FAST_ARITH,
+                    DRRT_NO_WARP_AGGREGATION, DRRT_REFERENCE_ARITH, DRRT_SOA)
 
 __all__ = [
     "trace", "trace_pln", "trace_target", "trace_sdf", "trace_cable", "backtrace",
@@ -28,10 +29,16 @@ __all__ = [
 
 
 def make_flags(reference_arith: bool = False, deterministic: bool = False,
-               accumulate: bool = False) -> int:
+               accumulate: bool = False, fast_arith: bool = False,
+               warp_aggregation: bool = True) -> int:
+    """Flag word of the C ABI (include/drrt_b200.h).  Default arithmetic = exact trajectory."""
+    if reference_arith and fast_arith:
+        raise ValueError("reference_arith and fast_arith are mutually exclusive")
     return ((DRRT_REFERENCE_ARITH if reference_arith else 0)
             | (DRRT_DETERMINISTIC if deterministic else 0)
-            | (DRRT_ACCUMULATE if accumulate else 0))
+            | (DRRT_ACCUMULATE if accumulate else 0)
+            | (DRRT_FAST_ARITH if fast_arith else 0)
+            | (0 if warp_aggregation else DRRT_NO_WARP_AGGREGATION))
 
 
 def new_stats(device) -> torch.Tensor:

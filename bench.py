@@ -336,13 +336,13 @@ def run_ours(args):
                 "workload": f"caustic-256 (BASELINE.json configs[3]): {NG}^3 bump IOR grid, {SENSOR}^2 = {n_rays} collimated rays per GPU, ds = h/2, seeds dx=dv=1",
                 "rays_per_gpu": n_rays, "grid": [NG, NG, NG], "parallelism": f"rays-dp{world} + grad allreduce" if world > 1 else "single GPU",
                 "l2": "no explicit flush: per-step working set (rays in/out 302 MB + grid 67 MB + gradient 67 MB) exceeds the 126 MB L2; the 67 MB IOR grid staying L2-resident across the step is the design",
-                "arithmetic": "factored polynomial (default)", "ray_steps_fwd": s_f, "ray_steps_adj": s_b,
+                "arithmetic": "exact trajectory (default flags=0): ray path bit-identical to the float32 reference formulas", "ray_steps_fwd": s_f, "ray_steps_adj": s_b,
                 "rays_not_exited": not_exited,
             },
             "fwd_ms": fwd_ms, "adj_ms": adj_ms,
             "fwd_ray_steps_per_s": s_f / (fwd_ms * 1e-3), "adj_ray_steps_per_s": s_b / (adj_ms * 1e-3),
             "roofline": {
-                "bound": "hbm", "kernel": "backtrace_kernel<sdf=0,ref=0,AccumFloat>", "achieved": adj_gbs, "peak": peak,
+                "bound": "hbm", "kernel": "backtrace_kernel<sdf=0,A_EXACT,AccumFloat,warp_agg=1>", "achieved": adj_gbs, "peak": peak,
                 "unit": "GB/s", "frac": adj_gbs / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_ray_step": BYTES_ADJ,
                 "fwd_kernel": {"achieved": fwd_gbs, "frac": fwd_gbs / peak, "algorithmic_bytes_per_ray_step": BYTES_FWD},

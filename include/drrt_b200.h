@@ -52,11 +52,24 @@ enum { DRRT_SOA = 1, DRRT_AOS = 3 };
 
 /* flags (bitwise or) */
 enum {
-  /* Arithmetic in the reference's exact operation order with no FMA contraction
-   * (bit-identical ray endpoints to a float32 CPU evaluation of the reference
-   * formulas).  Default is the factored per-cell polynomial form, which is
-   * algebraically identical and ~2x cheaper but rounds differently. */
+  /* Arithmetic.  Default (neither bit set): "exact trajectory" -- everything that
+   * decides where a ray goes (cell lookup, n, grad n, the v and x updates, every
+   * branch) is evaluated in the reference's literal operation order with no FMA
+   * contraction, so ray endpoints, directions and the cells visited are
+   * bit-identical to a float32 CPU evaluation of the reference formulas; the
+   * terms that only feed the linear gradient accumulation (Hessian, splat
+   * weights, lambda/mu updates) use factored FMA forms, which changes the
+   * gradient at the 1e-6 relative level (same class as atomic reordering).
+   * DRRT_REFERENCE_ARITH: literal operation order everywhere, 16 atomics per
+   * step like the reference (slow; for audits).
+   * DRRT_FAST_ARITH: the trilinear cell as a factored polynomial everywhere
+   * (~1.5x faster forward); float32 rounding then differs from the reference and a
+   * few rays per 10^4 take the other branch at a cell face. */
   DRRT_REFERENCE_ARITH = 1u << 0,
+  DRRT_FAST_ARITH = 1u << 3,
+  /* Adjoint only: issue every lane's atomics itself instead of pre-summing lanes
+   * that hit the same cell (A/B switch for profiling). */
+  DRRT_NO_WARP_AGGREGATION = 1u << 4,
   /* Adjoint only: accumulate the gradient in 64-bit fixed point so the result is
    * bit-stable from run to run regardless of atomic ordering. */
   DRRT_DETERMINISTIC = 1u << 1,
