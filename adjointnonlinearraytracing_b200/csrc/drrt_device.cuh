@@ -165,6 +165,84 @@ __device__ __forceinline__ void eval_grad_ref(const GridP &g, const float v[8], 
   nx.x = mul_(gx, g.rcp_h); nx.y = mul_(gy, g.rcp_h); nx.z = mul_(gz, g.rcp_h);
 }
 
+// ---------------------------------------------------------------------------
+// Packed FP32 (Blackwell FMUL2 / FFMA2: two independent IEEE-rounded float
+// operations per issue slot).  The kernels are issue-bound on the literal
+// reference arithmetic (profiles/r02_fwd_full.txt: 86 % issue-active, 64 of ~150
+// instructions per step are FMULs), so the multiplies are paired up.
+// ptxas contracts mul.rn.f32x2 feeding add/sub.rn.f32x2 into FFMA2 even with
+// explicit .rn and --fmad=false (checked in SASS), which would change the
+// rounding; packed products are therefore only ever consumed by further packed
+// multiplies or by SCALAR add.rn.f32, which ptxas never contracts.
+// ---------------------------------------------------------------------------
+typedef unsigned long long f32x2;
+
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ float lo2(f32x2 v) {
+  float lo, hi;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+  return lo;
+}
+__device__ __forceinline__ float hi2(f32x2 v) {
+  float lo, hi;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+  return hi;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 mul2s(f32x2 a, float b) { return mul2(a, pk2(b, b)); }
+// contraction allowed / intended (non-literal arithmetic only)
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+
+// Corner values as x-adjacent pairs: V[j] = (v[2j], v[2j+1]) = (x0, x1) at
+// (y,z) = (0,0), (1,0), (0,1), (1,1).
+__device__ __forceinline__ void load_corner_pairs(const GridP &g, const CellAddr &a, f32x2 V[4]) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) V[j] = pk2(__ldg(g.data + a.at(2 * j)), __ldg(g.data + a.at(2 * j + 1)));
+}
+
+// volume::eval_grad, src/volume.cpp:152-178 -- same operations, same order and
+// same roundings as eval_grad_ref above, with the 64 multiplies issued as 30
+// FMUL2 (+3 FMUL); every add is a scalar FADD in the reference's order.
+__device__ __forceinline__ void eval_grad_ref_x2(const GridP &g, const f32x2 V[4], float w0x, float w0y,
+                                                 float w0z, float &n, f3 &nx) {
+  const float w1x = sub_(1.0f, w0x), w1y = sub_(1.0f, w0y), w1z = sub_(1.0f, w0z);
+  const f32x2 A = pk2(w1x, w0x);
+  // n = sum_k w_k v_k, w_ijk = (wx_i * wy_j) * wz_k
+  const f32x2 Py0 = mul2s(A, w1y), Py1 = mul2s(A, w0y);
+  const f32x2 T00 = mul2(mul2s(Py0, w1z), V[0]), T10 = mul2(mul2s(Py1, w1z), V[1]);
+  const f32x2 T01 = mul2(mul2s(Py0, w0z), V[2]), T11 = mul2(mul2s(Py1, w0z), V[3]);
+  float s = lo2(T00);
+  s = add_(s, hi2(T00)); s = add_(s, lo2(T10)); s = add_(s, hi2(T10));
+  s = add_(s, lo2(T01)); s = add_(s, hi2(T01)); s = add_(s, lo2(T11)); s = add_(s, hi2(T11));
+  n = s;
+  // d/dx: (v * wy) * wz, hi = x1 (plus), lo = x0 (minus)
+  const f32x2 X00 = mul2s(mul2s(V[0], w1y), w1z), X01 = mul2s(mul2s(V[2], w1y), w0z);
+  const f32x2 X10 = mul2s(mul2s(V[1], w0y), w1z), X11 = mul2s(mul2s(V[3], w0y), w0z);
+  const float gx = sub_(add_(add_(add_(hi2(X00), hi2(X01)), hi2(X10)), hi2(X11)),
+                        add_(add_(add_(lo2(X00), lo2(X01)), lo2(X10)), lo2(X11)));
+  // d/dy and d/dz share the first products v * wx
+  const f32x2 F00 = mul2(V[0], A), F10 = mul2(V[1], A), F01 = mul2(V[2], A), F11 = mul2(V[3], A);
+  const f32x2 G10 = mul2s(F10, w1z), G11 = mul2s(F11, w0z), G00 = mul2s(F00, w1z), G01 = mul2s(F01, w0z);
+  const float gy = sub_(add_(add_(add_(lo2(G10), lo2(G11)), hi2(G10)), hi2(G11)),
+                        add_(add_(add_(lo2(G00), lo2(G01)), hi2(G00)), hi2(G01)));
+  const f32x2 H01 = mul2s(F01, w1y), H11 = mul2s(F11, w0y), H00 = mul2s(F00, w1y), H10 = mul2s(F10, w0y);
+  const float gz = sub_(add_(add_(add_(lo2(H01), lo2(H11)), hi2(H01)), hi2(H11)),
+                        add_(add_(add_(lo2(H00), lo2(H10)), hi2(H00)), hi2(H10)));
+  nx.x = mul_(gx, g.rcp_h); nx.y = mul_(gy, g.rcp_h); nx.z = mul_(gz, g.rcp_h);
+}
+
 // enoki lerp(a,b,t) = fmadd(b, t, fnmadd(a, t, a))
 __device__ __forceinline__ float lerp_ref(float a, float b, float t) { return fma_(b, t, fma_(-a, t, a)); }
 

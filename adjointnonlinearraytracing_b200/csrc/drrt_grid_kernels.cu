@@ -34,11 +34,14 @@ struct CellCache;
 template <>
 struct CellCache<A_REF> {
   int cx = INT_MIN, cy = 0, cz = 0;
-  float v[8];
-  __device__ __forceinline__ void refill(const GridP &g, const CellAddr &a) { load_corners(g, a, v); }
+  f32x2 V[4];  // x-adjacent corner pairs
+  __device__ __forceinline__ void refill(const GridP &g, const CellAddr &a) { load_corner_pairs(g, a, V); }
   __device__ __forceinline__ void eval(const GridP &g, const CellIdx &c, float &n, f3 &nx, f3 *hm) const {
-    eval_grad_ref(g, v, c.wx, c.wy, c.wz, n, nx);
-    if (hm) *hm = eval_hess_ref(g, v, c.wx, c.wy, c.wz);
+    eval_grad_ref_x2(g, V, c.wx, c.wy, c.wz, n, nx);
+    if (hm) {
+      const float v[8] = {lo2(V[0]), hi2(V[0]), lo2(V[1]), hi2(V[1]), lo2(V[2]), hi2(V[2]), lo2(V[3]), hi2(V[3])};
+      *hm = eval_hess_ref(g, v, c.wx, c.wy, c.wz);
+    }
   }
 };
 
@@ -66,17 +69,17 @@ struct CellCache<A_FAST> {
 template <>
 struct CellCache<A_EXACT> {
   int cx = INT_MIN, cy = 0, cz = 0;
-  float v[8];
+  f32x2 V[4];  // x-adjacent corner pairs
   // mixed second differences in the reference's association order
   // (src/volume.cpp:79-90; they cancel to ~1e-4 of the voxel values, so the order
   // of the subtractions matters at the 1e-3 relative level), pre-scaled by 1/h^2:
   // d?0 at w = 0 and the slope d?1 - d?0.
   float hxy0, hxys, hxz0, hxzs, hyz0, hyzs;
   __device__ __forceinline__ void refill(const GridP &g, const CellAddr &a) {
-    load_corners(g, a, v);
+    load_corner_pairs(g, a, V);
     const float r2 = mul_(g.rcp_h, g.rcp_h);
-    const float v000 = v[0], v100 = v[1], v010 = v[2], v110 = v[3];
-    const float v001 = v[4], v101 = v[5], v011 = v[6], v111 = v[7];
+    const float v000 = lo2(V[0]), v100 = hi2(V[0]), v010 = lo2(V[1]), v110 = hi2(V[1]);
+    const float v001 = lo2(V[2]), v101 = hi2(V[2]), v011 = lo2(V[3]), v111 = hi2(V[3]);
     float a0 = add_(sub_(sub_(v110, v010), v100), v000), a1 = add_(sub_(sub_(v111, v011), v101), v001);
     float b0 = add_(sub_(sub_(v101, v001), v100), v000), b1 = add_(sub_(sub_(v111, v011), v110), v010);
     float c0 = add_(sub_(sub_(v011, v001), v010), v000), c1 = add_(sub_(sub_(v111, v101), v110), v100);
@@ -85,7 +88,7 @@ struct CellCache<A_EXACT> {
     hyz0 = c0 * r2; hyzs = (c1 - c0) * r2;
   }
   __device__ __forceinline__ void eval(const GridP &g, const CellIdx &c, float &n, f3 &nx, f3 *hm) const {
-    eval_grad_ref(g, v, c.wx, c.wy, c.wz, n, nx);
+    eval_grad_ref_x2(g, V, c.wx, c.wy, c.wz, n, nx);
     if (hm) {
       hm->x = fmaf(hxys, c.wz, hxy0);
       hm->y = fmaf(hxzs, c.wy, hxz0);
