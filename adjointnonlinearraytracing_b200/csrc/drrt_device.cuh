@@ -77,16 +77,19 @@ __device__ __forceinline__ bool escaped(const GridP &g, f3 p, f3 v) {
 // Cell lookup, src/volume.cpp:128-141: fractional weights from the UNCLAMPED
 // floor, both corner indices clamped to [0, res-1].
 struct CellIdx {
-  int cx, cy, cz;     // unclamped floor(p / h)
+  float fx, fy, fz;   // unclamped floor(p / h), kept as floats: the per-step "same cell?" test
+                      // compares these, the integer conversion happens only on a refill
   float wx, wy, wz;   // w0
+  __device__ __forceinline__ int cx() const { return (int) fx; }
+  __device__ __forceinline__ int cy() const { return (int) fy; }
+  __device__ __forceinline__ int cz() const { return (int) fz; }
 };
 
 __device__ __forceinline__ CellIdx cell_of(const GridP &g, f3 p) {
   CellIdx c;
   float px = mul_(p.x, g.rcp_h), py = mul_(p.y, g.rcp_h), pz = mul_(p.z, g.rcp_h);
-  float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
-  c.cx = (int) fx; c.cy = (int) fy; c.cz = (int) fz;
-  c.wx = sub_(px, fx); c.wy = sub_(py, fy); c.wz = sub_(pz, fz);
+  c.fx = floorf(px); c.fy = floorf(py); c.fz = floorf(pz);
+  c.wx = sub_(px, c.fx); c.wy = sub_(py, c.fy); c.wz = sub_(pz, c.fz);
   return c;
 }
 
@@ -185,11 +188,13 @@ __device__ __forceinline__ f32x2 pk2(float lo, float hi) {
 __device__ __forceinline__ float lo2(f32x2 v) {
   float lo, hi;
   asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+  (void) hi;
   return lo;
 }
 __device__ __forceinline__ float hi2(f32x2 v) {
   float lo, hi;
   asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+  (void) lo;
   return hi;
 }
 __device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
@@ -210,6 +215,28 @@ __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
 __device__ __forceinline__ void load_corner_pairs(const GridP &g, const CellAddr &a, f32x2 V[4]) {
 #pragma unroll
   for (int j = 0; j < 4; ++j) V[j] = pk2(__ldg(g.data + a.at(2 * j)), __ldg(g.data + a.at(2 * j + 1)));
+}
+
+// Address + gather of one cell.  Cells strictly inside the grid (all but the rays'
+// first and last steps) take the fast path: unit strides, four row pointers, the
+// x+1 neighbour as an immediate offset.
+__device__ __forceinline__ CellAddr gather_cell(const GridP &g, int cx, int cy, int cz, f32x2 V[4]) {
+  CellAddr a;
+  const bool interior = ((unsigned) cx < (unsigned) (g.W - 1)) & ((unsigned) cy < (unsigned) (g.H - 1)) &
+                        ((unsigned) cz < (unsigned) (g.D - 1));
+  if (interior) {
+    a.base = (cz * g.H + cy) * g.W + cx;
+    a.dx = 1; a.dy = g.W; a.dz = g.H * g.W;
+    const float *p00 = g.data + a.base, *p10 = p00 + a.dy, *p01 = p00 + a.dz, *p11 = p01 + a.dy;
+    V[0] = pk2(__ldg(p00), __ldg(p00 + 1));
+    V[1] = pk2(__ldg(p10), __ldg(p10 + 1));
+    V[2] = pk2(__ldg(p01), __ldg(p01 + 1));
+    V[3] = pk2(__ldg(p11), __ldg(p11 + 1));
+  } else {
+    a = corner_addr(g, cx, cy, cz);
+    load_corner_pairs(g, a, V);
+  }
+  return a;
 }
 
 // volume::eval_grad, src/volume.cpp:152-178 -- same operations, same order and
@@ -347,6 +374,22 @@ __device__ __forceinline__ void splat_accumulate(float val, f3 gr, float wx, flo
   acc[5] = fmaf(wx, C01, fmaf(A1, B01, acc[5]));
   acc[6] = fmaf(ux, C11, fmaf(A0, B11, acc[6]));
   acc[7] = fmaf(wx, C11, fmaf(A1, B11, acc[7]));
+}
+
+// The same fused splat on x-adjacent accumulator pairs P[j] = (acc[2j], acc[2j+1])
+// with FFMA2 (contraction is intended here: this is not the literal arithmetic).
+__device__ __forceinline__ void splat_accumulate_x2(float val, f3 gr, float wx, float wy, float wz,
+                                                    f32x2 P[4]) {
+  const float ux = 1.0f - wx, uy = 1.0f - wy, uz = 1.0f - wz;
+  const f32x2 X = pk2(ux, wx);
+  const f32x2 A = fma2(pk2(val, val), X, pk2(-gr.x, gr.x));
+  const float B00 = uy * uz, B10 = wy * uz, B01 = uy * wz, B11 = wy * wz;
+  const float gyuz = gr.y * uz, gywz = gr.y * wz, gzuy = gr.z * uy, gzwy = gr.z * wy;
+  const float C00 = -gyuz - gzuy, C10 = gyuz - gzwy, C01 = gzuy - gywz, C11 = gywz + gzwy;
+  P[0] = fma2(X, pk2(C00, C00), fma2(A, pk2(B00, B00), P[0]));
+  P[1] = fma2(X, pk2(C10, C10), fma2(A, pk2(B10, B10), P[1]));
+  P[2] = fma2(X, pk2(C01, C01), fma2(A, pk2(B01, B01), P[2]));
+  P[3] = fma2(X, pk2(C11, C11), fma2(A, pk2(B11, B11), P[3]));
 }
 
 // ---------------------------------------------------------------------------

@@ -27,15 +27,28 @@ enum { K_PLAIN = 0, K_PLANE = 1, K_TARGET = 2, K_SDF = 3 };
 //             Hessian, splat weights, lambda/mu -- in factored FMA form.
 enum { A_FAST = 0, A_REF = 1, A_EXACT = 2 };
 
-// Register cache of the cell a ray is in.
+// Register cache of the cell a ray is in: the floor coordinates it was filled for
+// (floats; NaN = empty, so the first comparison reports a change) and the cell's
+// data in the form the arithmetic flavour wants.
+struct CellTag {
+  float fx, fy, fz;
+  __device__ __forceinline__ void reset() { fx = __int_as_float(0x7fc00000); fy = fz = 0.f; }
+  __device__ __forceinline__ bool differs(const CellIdx &c) const {
+    return (c.fx != fx) | (c.fy != fy) | (c.fz != fz);
+  }
+  __device__ __forceinline__ void set(const CellIdx &c) { fx = c.fx; fy = c.fy; fz = c.fz; }
+};
+
 template <int AR>
 struct CellCache;
 
 template <>
-struct CellCache<A_REF> {
-  int cx = INT_MIN, cy = 0, cz = 0;
+struct CellCache<A_REF> : CellTag {
   f32x2 V[4];  // x-adjacent corner pairs
-  __device__ __forceinline__ void refill(const GridP &g, const CellAddr &a) { load_corner_pairs(g, a, V); }
+  __device__ __forceinline__ CellAddr refill(const GridP &g, const CellIdx &c) {
+    set(c);
+    return gather_cell(g, c.cx(), c.cy(), c.cz(), V);
+  }
   __device__ __forceinline__ void eval(const GridP &g, const CellIdx &c, float &n, f3 &nx, f3 *hm) const {
     eval_grad_ref_x2(g, V, c.wx, c.wy, c.wz, n, nx);
     if (hm) {
@@ -46,13 +59,15 @@ struct CellCache<A_REF> {
 };
 
 template <>
-struct CellCache<A_FAST> {
-  int cx = INT_MIN, cy = 0, cz = 0;
+struct CellCache<A_FAST> : CellTag {
   CellPoly p;
-  __device__ __forceinline__ void refill(const GridP &g, const CellAddr &a) {
-    float v[8];
-    load_corners(g, a, v);
+  __device__ __forceinline__ CellAddr refill(const GridP &g, const CellIdx &c) {
+    set(c);
+    f32x2 V[4];
+    CellAddr a = gather_cell(g, c.cx(), c.cy(), c.cz(), V);
+    const float v[8] = {lo2(V[0]), hi2(V[0]), lo2(V[1]), hi2(V[1]), lo2(V[2]), hi2(V[2]), lo2(V[3]), hi2(V[3])};
     p = make_poly(v);
+    return a;
   }
   // nx and hm are returned in world units
   __device__ __forceinline__ void eval(const GridP &g, const CellIdx &c, float &n, f3 &nx, f3 *hm) const {
@@ -67,16 +82,16 @@ struct CellCache<A_FAST> {
 };
 
 template <>
-struct CellCache<A_EXACT> {
-  int cx = INT_MIN, cy = 0, cz = 0;
+struct CellCache<A_EXACT> : CellTag {
   f32x2 V[4];  // x-adjacent corner pairs
   // mixed second differences in the reference's association order
   // (src/volume.cpp:79-90; they cancel to ~1e-4 of the voxel values, so the order
   // of the subtractions matters at the 1e-3 relative level), pre-scaled by 1/h^2:
   // d?0 at w = 0 and the slope d?1 - d?0.
   float hxy0, hxys, hxz0, hxzs, hyz0, hyzs;
-  __device__ __forceinline__ void refill(const GridP &g, const CellAddr &a) {
-    load_corner_pairs(g, a, V);
+  __device__ __forceinline__ CellAddr refill(const GridP &g, const CellIdx &c) {
+    set(c);
+    CellAddr a = gather_cell(g, c.cx(), c.cy(), c.cz(), V);
     const float r2 = mul_(g.rcp_h, g.rcp_h);
     const float v000 = lo2(V[0]), v100 = hi2(V[0]), v010 = lo2(V[1]), v110 = hi2(V[1]);
     const float v001 = lo2(V[2]), v101 = hi2(V[2]), v011 = lo2(V[3]), v111 = hi2(V[3]);
@@ -86,6 +101,7 @@ struct CellCache<A_EXACT> {
     hxy0 = a0 * r2; hxys = (a1 - a0) * r2;
     hxz0 = b0 * r2; hxzs = (b1 - b0) * r2;
     hyz0 = c0 * r2; hyzs = (c1 - c0) * r2;
+    return a;
   }
   __device__ __forceinline__ void eval(const GridP &g, const CellIdx &c, float &n, f3 &nx, f3 *hm) const {
     eval_grad_ref_x2(g, V, c.wx, c.wy, c.wz, n, nx);
@@ -97,19 +113,11 @@ struct CellCache<A_EXACT> {
   }
 };
 
-template <int AR>
-__device__ __forceinline__ bool cell_changed(const CellCache<AR> &cc, const CellIdx &c) {
-  return (c.cx != cc.cx) | (c.cy != cc.cy) | (c.cz != cc.cz);
-}
-
 // Trilinear value only (sdf lookups), src/volume.cpp:162-163 under the caller's mask.
 template <int AR>
 __device__ __forceinline__ float eval_value(const GridP &g, CellCache<AR> &cc, f3 x) {
   CellIdx c = cell_of(g, x);
-  if (cell_changed(cc, c)) {
-    cc.refill(g, corner_addr(g, c.cx, c.cy, c.cz));
-    cc.cx = c.cx; cc.cy = c.cy; cc.cz = c.cz;
-  }
+  if (cc.differs(c)) cc.refill(g, c);
   float n; f3 nx;
   cc.eval(g, c, n, nx, nullptr);
   return n;
@@ -129,7 +137,7 @@ __global__ void __launch_bounds__(kTraceThreads) trace_kernel(TraceArgs a) {
   constexpr bool REF = AR != A_FAST;
   const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
   const bool valid = r < a.N;
-  int64_t steps = 0;
+  int steps = 0;  // per ray < max_steps < 2^31
   int not_exited = 0;
   if (valid) {
     const GridP g = a.grid;
@@ -141,26 +149,23 @@ __global__ void __launch_bounds__(kTraceThreads) trace_kernel(TraceArgs a) {
     if (KIND == K_PLANE) { aux0 = ld3(a.aux0, r, a.N, a.layout); aux1 = ld3(a.aux1, r, a.N, a.layout); }
     if (KIND == K_TARGET) { aux0 = ld3(a.aux0, r, a.N, a.layout); best = dist2_ref(x, aux0); }
     bool inside = inbounds(g, x);  // :61
-    bool esc = false;
+    bool esc = false, crossed = false;
     CellCache<AR> cc;
     CellCache<AR> sc;  // sdf grid (K_SDF only)
+    cc.reset(); sc.reset();
     GridP sg = g;
     sg.data = a.sdf;
     int i = 0;
     for (; i < a.max_steps; ++i) {
       if (inside) {  // masked gather: outside lanes see n = 0, grad n = 0 and fly straight
         CellIdx c = cell_of(g, x);
-        if (cell_changed(cc, c)) {
-          cc.refill(g, corner_addr(g, c.cx, c.cy, c.cz));
-          cc.cx = c.cx; cc.cy = c.cy; cc.cz = c.cz;
-        }
+        if (cc.differs(c)) cc.refill(g, c);
         float n; f3 nx;
         cc.eval(g, c, n, nx, nullptr);
         float dsn = REF ? mul_(ds, n) : ds * n;
         v.x = fmaf(dsn, nx.x, v.x); v.y = fmaf(dsn, nx.y, v.y); v.z = fmaf(dsn, nx.z, v.z);  // :70
       }
       x.x = fmaf(ds, v.x, x.x); x.y = fmaf(ds, v.y, x.y); x.z = fmaf(ds, v.z, x.z);  // :71
-      ++steps;
       const bool inb = inbounds(g, x);
       bool cur_inside = inb;  // :73
       if (KIND == K_PLANE) {  // :144-145
@@ -176,13 +181,15 @@ __global__ void __launch_bounds__(kTraceThreads) trace_kernel(TraceArgs a) {
       if (KIND == K_TARGET) {  // :216-227
         float cur = dist2_ref(x, aux0);
         if (cur < best) { xt = x; vt = v; best = cur; }
-      } else if (cross) {  // :79-80
-        xt = x; vt = v;
       }
       esc = cross | (!inb && escaped(g, x, v));  // :75-76 (escaped() implies !inbounds)
       inside = cur_inside;  // :86
-      if (esc) { ++i; break; }
+      // :79-80 capture: a crossing always ends the ray's loop, so (x, v) at the break
+      // ARE the captured exit state; the copy is done once after the loop.
+      if (esc) { crossed = cross; ++i; break; }
     }
+    steps = i;
+    if (KIND != K_TARGET && crossed) { xt = x; vt = v; }
     if (!esc) {
       not_exited = 1;
       if (KIND == K_PLAIN || KIND == K_PLANE) xt = x;  // :95, :167 (vt keeps the launch value)
@@ -200,10 +207,10 @@ __global__ void __launch_bounds__(kTraceThreads) trace_kernel(TraceArgs a) {
     }
   }
   if (a.stats) {
-    steps = warp_sum_i64(steps);
+    const int64_t wsteps = warp_sum_i64((int64_t) steps);
     int ne = __reduce_add_sync(0xffffffffu, not_exited);
     if ((threadIdx.x & 31) == 0) {
-      if (steps) atomicAdd((unsigned long long *) a.stats, (unsigned long long) steps);
+      if (wsteps) atomicAdd((unsigned long long *) a.stats, (unsigned long long) wsteps);
       if (ne) atomicAdd((unsigned long long *) a.stats + 1, (unsigned long long) ne);
     }
   }
@@ -261,17 +268,24 @@ constexpr int kAggRun = 8;   // maximum run length (aligned), log2 shuffle round
 constexpr int kAggMin = 4;   // fewer flushing lanes than this: plain atomics
 
 template <class Accum>
-__device__ __forceinline__ void flush_direct(const Accum &out, const CellAddr &ca, float acc[8]) {
+__device__ __forceinline__ void flush_direct(const Accum &out, const CellAddr &ca, const float acc[8]) {
 #pragma unroll
   for (int k = 0; k < 8; ++k) out.add(ca.at(k), acc[k]);
 }
 
+__device__ __forceinline__ void unpack8(const f32x2 P[4], float acc[8]) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { acc[2 * j] = lo2(P[j]); acc[2 * j + 1] = hi2(P[j]); }
+}
+
 // Warp-uniform: every lane of the warp calls this with its own `fl`.
 template <class Accum>
-__device__ __forceinline__ void flush_aggregated(const Accum &out, const CellAddr &ca, float acc[8],
+__device__ __forceinline__ void flush_aggregated(const Accum &out, const CellAddr &ca, const f32x2 P[4],
                                                  bool fl, unsigned lane) {
   const unsigned fm = __ballot_sync(kFull, fl);
   if (fm == 0) return;
+  float acc[8];
+  unpack8(P, acc);
   if (__popc(fm) < kAggMin) {
     if (fl) flush_direct(out, ca, acc);
     return;
@@ -305,13 +319,14 @@ __global__ void __launch_bounds__(kAdjThreads) backtrace_kernel(AdjArgs a, Accum
   const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned lane = threadIdx.x & 31;
   const bool valid = r < a.N;
-  int64_t steps = 0;
+  int steps = 0;  // per ray < max_steps < 2^31
   const GridP g = a.grid;
   const float ds = a.ds;
   f3 x = {0, 0, 0}, v = {0, 0, 0}, la = {0, 0, 0}, mu = {0, 0, 0};
   bool active = false;
   CellCache<AR> cc;
   CellCache<AR> sc;
+  cc.reset(); sc.reset();
   GridP sg = g;
   sg.data = a.sdf;
   bool outside = false;
@@ -327,9 +342,7 @@ __global__ void __launch_bounds__(kAdjThreads) backtrace_kernel(AdjArgs a, Accum
     }
   }
   CellAddr ca = {0, 0, 0, 0};
-  float acc[8];
-#pragma unroll
-  for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+  f32x2 P[4] = {0ull, 0ull, 0ull, 0ull};  // accumulator pairs (acc[2j], acc[2j+1])
   bool have = false;
   for (int i = 0; i < a.max_steps; ++i) {
     if (AGG) {
@@ -337,29 +350,29 @@ __global__ void __launch_bounds__(kAdjThreads) backtrace_kernel(AdjArgs a, Accum
     } else if (!active) {
       break;
     }
-    CellIdx c = {0, 0, 0, 0.f, 0.f, 0.f};
+    CellIdx c = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     bool chg = false;
     if (active) {
       x.x = fmaf(-ds, v.x, x.x); x.y = fmaf(-ds, v.y, x.y); x.z = fmaf(-ds, v.z, x.z);  // :420
       c = cell_of(g, x);
-      chg = cell_changed(cc, c);
+      chg = cc.differs(c);
     }
     if (!REF) {
       const bool fl = have && (chg || !active);
-      if (AGG) flush_aggregated(out, ca, acc, fl, lane);
-      else if (fl) flush_direct(out, ca, acc);
+      if (AGG) {
+        flush_aggregated(out, ca, P, fl, lane);
+      } else if (fl) {
+        float acc[8];
+        unpack8(P, acc);
+        flush_direct(out, ca, acc);
+      }
       if (fl) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+        P[0] = P[1] = P[2] = P[3] = 0ull;
         have = false;
       }
     }
     if (active) {
-      if (chg) {
-        ca = corner_addr(g, c.cx, c.cy, c.cz);
-        cc.refill(g, ca);
-        cc.cx = c.cx; cc.cy = c.cy; cc.cz = c.cz;
-      }
+      if (chg) ca = cc.refill(g, c);
       float n; f3 nx, hm;
       cc.eval(g, c, n, nx, &hm);  // :421-422 (same 8 voxels serve grad and Hessian)
       float mdsn = TRAJ_REF ? mul_(-ds, n) : -ds * n;
@@ -394,7 +407,7 @@ __global__ void __launch_bounds__(kAdjThreads) backtrace_kernel(AdjArgs a, Accum
           float dn = fmaf(mu.z, nx.z, fmaf(mu.y, nx.y, mu.x * nx.x));
           float nds = n * ds;
           f3 dnx = {nds * mu.x, nds * mu.y, nds * mu.z};
-          splat_accumulate(dn * ds, dnx, c.wx, c.wy, c.wz, acc);
+          splat_accumulate_x2(dn * ds, dnx, c.wx, c.wy, c.wz, P);
           have = true;
           float nhxy = n * hm.x, nhxz = n * hm.y, nhyz = n * hm.z;
           float h0 = fmaf(nhxz, mu.z, nhxy * mu.y);
@@ -409,12 +422,17 @@ __global__ void __launch_bounds__(kAdjThreads) backtrace_kernel(AdjArgs a, Accum
     }
   }
   if (!REF) {
-    if (AGG) flush_aggregated(out, ca, acc, have, lane);
-    else if (have) flush_direct(out, ca, acc);
+    if (AGG) {
+      flush_aggregated(out, ca, P, have, lane);
+    } else if (have) {
+      float acc[8];
+      unpack8(P, acc);
+      flush_direct(out, ca, acc);
+    }
   }
   if (a.stats) {
-    steps = warp_sum_i64(steps);
-    if (lane == 0 && steps) atomicAdd((unsigned long long *) a.stats, (unsigned long long) steps);
+    const int64_t wsteps = warp_sum_i64((int64_t) steps);
+    if (lane == 0 && wsteps) atomicAdd((unsigned long long *) a.stats, (unsigned long long) wsteps);
   }
 }
 

@@ -59,7 +59,7 @@ __global__ void volume_eval_kernel(GridP g, const float *pos, int64_t N, int lay
   CellIdx c = cell_of(g, p);
   int idx[8];
   float v[8];
-  corner_indices(g, c.cx, c.cy, c.cz, idx);
+  corner_indices(g, c.cx(), c.cy(), c.cz(), idx);
   load_corners(g, idx, v);
   float nn; f3 nx, hm;
   if (REF) {
@@ -87,7 +87,7 @@ __global__ void volume_splat_kernel(GridP g, float *data, const float *pos, cons
   f3 p = ld3(pos, r, N, layout), gr = ld3(grad, r, N, layout);
   CellIdx c = cell_of(g, p);
   int idx[8];
-  corner_indices(g, c.cx, c.cy, c.cz, idx);
+  corner_indices(g, c.cx(), c.cy(), c.cz(), idx);
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   splat_accumulate(val[r], gr, c.wx, c.wy, c.wz, acc);
 #pragma unroll
