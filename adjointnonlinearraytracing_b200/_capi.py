@@ -18,7 +18,17 @@ DRRT_REFERENCE_ARITH = 1 << 0
 DRRT_DETERMINISTIC = 1 << 1
 DRRT_ACCUMULATE = 1 << 2
 DRRT_FAST_ARITH = 1 << 3
-DRRT_NO_WARP_AGGREGATION = 1 << 4
+DRRT_WARP_AGGREGATION = 1 << 4
+DRRT_NO_INTERLEAVE = 1 << 5
+
+
+def DRRT_AGG_RUN(n: int) -> int:
+    return int(n) << 8
+
+
+def DRRT_INTERLEAVE(n: int) -> int:
+    return int(n) << 12
+
 DRRT_UNIQUE_ID_BYTES = 128
 
 # every symbol include/drrt_b200.h declares (checked by tests/test_capi_symbols.py)

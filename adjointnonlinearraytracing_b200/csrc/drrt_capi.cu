@@ -97,6 +97,13 @@ int check_rays(int64_t N, int layout, float ds) {
 
 constexpr size_t kFixedTail = 16;
 
+// 0 = off, -1 = measured on the device (default), 2^k = forced (DRRT_INTERLEAVE(n))
+int interleave_of(unsigned flags) {
+  if (flags & DRRT_NO_INTERLEAVE) return 0;
+  unsigned n = (flags >> 12) & 0x3fu;
+  return n ? (int) n : -1;
+}
+
 // 0 fast polynomial, 1 reference-literal, 2 exact-trajectory (default)
 int arith_of(unsigned flags) {
   if (flags & DRRT_REFERENCE_ARITH) return 1;
@@ -157,6 +164,7 @@ int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, i
   a.sdf = sdf; a.xt = xt; a.vt = vt; a.dx = dx; a.dv = dv;
   a.N = N; a.layout = layout; a.ds = ds; a.stats = stats;
   a.max_steps = cap_grid(2.0f, h, W, H, D, ds);
+  a.agg_policy = (int) ((flags >> 8) & 0xfu);  // experimental: DRRT_AGG_RUN(n), 0 = adaptive
   unsigned long long *fixed = nullptr;
   unsigned *max_bits = nullptr;
   if (det) {
@@ -165,7 +173,7 @@ int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, i
     CU_TRY(cudaMemsetAsync(scratch, 0, sizeof(unsigned long long) * (size_t) G + kFixedTail, s));
     g_launches += launch_fixed_max(dx, dv, 3 * N, max_bits, s);
   }
-  g_launches += launch_backtrace(sdf_kind, arith_of(flags), !(flags & DRRT_NO_WARP_AGGREGATION), a, grad, fixed, max_bits, s);
+  g_launches += launch_backtrace(sdf_kind, arith_of(flags), (flags & DRRT_WARP_AGGREGATION) != 0, interleave_of(flags), a, grad, fixed, max_bits, s);
   if (det) g_launches += launch_fixed_to_float(fixed, max_bits, grad, G, accumulate, s);
   return check_launch("backtrace");
 }

@@ -10,6 +10,8 @@
 // outputs can change again (gathers are masked to 0 outside, so it flies
 // straight away from a convex box).  trace_target is the exception -- see
 // trace_target_tail_kernel.
+#include <atomic>
+
 #include "drrt_device.cuh"
 #include "drrt_launch.h"
 
@@ -264,7 +266,7 @@ __global__ void __launch_bounds__(kTraceThreads) trace_target_tail_kernel(TraceA
 //   9.7 sectors per RED request) disappear.
 // ---------------------------------------------------------------------------
 constexpr unsigned kFull = 0xffffffffu;
-constexpr int kAggRun = 8;   // maximum run length (aligned), log2 shuffle rounds
+constexpr int kAdapt8 = 24, kAdapt4 = 12, kAdapt2 = 5;  // adaptive policy: average lanes per cell
 constexpr int kAggMin = 4;   // fewer flushing lanes than this: plain atomics
 
 template <class Accum>
@@ -278,28 +280,17 @@ __device__ __forceinline__ void unpack8(const f32x2 P[4], float acc[8]) {
   for (int j = 0; j < 4; ++j) { acc[2 * j] = lo2(P[j]); acc[2 * j + 1] = hi2(P[j]); }
 }
 
-// Warp-uniform: every lane of the warp calls this with its own `fl`.
-template <class Accum>
-__device__ __forceinline__ void flush_aggregated(const Accum &out, const CellAddr &ca, const f32x2 P[4],
-                                                 bool fl, unsigned lane) {
-  const unsigned fm = __ballot_sync(kFull, fl);
-  if (fm == 0) return;
-  float acc[8];
-  unpack8(P, acc);
-  if (__popc(fm) < kAggMin) {
-    if (fl) flush_direct(out, ca, acc);
-    return;
-  }
-  // two lanes address the same 8 voxels iff corner 0 and corner 7 coincide
-  const int k0 = fl ? ca.base : -1;
-  const int k7 = ca.base + ca.dx + ca.dy + ca.dz;
-  const int p0 = __shfl_up_sync(kFull, k0, 1), p7 = __shfl_up_sync(kFull, k7, 1);
-  const bool head = fl && ((lane & (kAggRun - 1)) == 0 || p0 != k0 || p7 != k7);
+// Segmented shuffle reduction over runs of consecutive flushing lanes that address
+// the same cell, runs cut at multiples of RUN lanes: log2(RUN) rounds of 8 SHFL +
+// 8 FADD.  Returns true on the lane that now holds its run's sum.
+template <int RUN>
+__device__ __forceinline__ bool reduce_runs(float acc[8], bool fl, bool first, unsigned lane) {
+  const bool head = first || (fl && (lane & (RUN - 1)) == 0);
   const unsigned stops = __ballot_sync(kFull, head || !fl);
   const unsigned above = stops & ~((2u << lane) - 1u);
   const int end = above ? __ffs(above) - 1 : 32;
 #pragma unroll
-  for (int off = 1; off < kAggRun; off <<= 1) {
+  for (int off = 1; off < RUN; off <<= 1) {
     const bool take = (int) (lane + off) < end;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
@@ -307,7 +298,95 @@ __device__ __forceinline__ void flush_aggregated(const Accum &out, const CellAdd
       if (take) acc[k] += t;
     }
   }
+  return head;
+}
+
+// Per-warp aggregation state: the run length in use and a flush-event counter.
+struct AggState {
+  int run, events;
+};
+
+// Warp-uniform: every lane of the warp calls this with its own `fl`.
+// `policy`: 2, 4, 8 = fixed maximum run length; 0 = adaptive.
+//
+// Measured (tools/gpu_tune_agg.py, profiles/r03_tune_agg.log): a same-address
+// conflict inside one RED costs less than a shuffle round until ~4 lanes collide,
+// so the best run length is about (lanes per cell) / 4: none at 4 rays per cell,
+// 2 at 8, 4 at 16, 8 at 32.  The adaptive policy re-measures the average number of
+// consecutive lanes per cell every 8th flush of the warp and picks accordingly.
+template <class Accum>
+__device__ __forceinline__ void flush_aggregated(const Accum &out, const CellAddr &ca, const f32x2 P[4],
+                                                 bool fl, unsigned lane, int policy, AggState &st) {
+  const unsigned fm = __ballot_sync(kFull, fl);
+  if (fm == 0) return;
+  float acc[8];
+  unpack8(P, acc);
+  const int nfl = __popc(fm);
+  const bool probe = policy == 0 && (st.events++ & 7) == 0;
+  if (policy != 0) st.run = policy;
+  if ((st.run == 1 && !probe) || nfl < kAggMin) {
+    if (fl) flush_direct(out, ca, acc);
+    return;
+  }
+  // two lanes address the same 8 voxels iff corner 0 and corner 7 coincide
+  const int k0 = fl ? ca.base : -1;
+  const int k7 = ca.base + ca.dx + ca.dy + ca.dz;
+  const int p0 = __shfl_up_sync(kFull, k0, 1), p7 = __shfl_up_sync(kFull, k7, 1);
+  const bool first = fl && (lane == 0 || p0 != k0 || p7 != k7);  // first lane of a same-cell run
+  if (probe) {
+    const int nruns = __popc(__ballot_sync(kFull, first));
+    st.run = (nfl >= kAdapt8 * nruns) ? 8 : (nfl >= kAdapt4 * nruns) ? 4 : (nfl >= kAdapt2 * nruns) ? 2 : 1;
+  }
+  bool head;
+  if (st.run == 8) head = reduce_runs<8>(acc, fl, first, lane);
+  else if (st.run == 4) head = reduce_runs<4>(acc, fl, first, lane);
+  else if (st.run == 2) head = reduce_runs<2>(acc, fl, first, lane);
+  else head = fl;
   if (head) flush_direct(out, ca, acc);
+}
+
+// ---------------------------------------------------------------------------
+// Ray interleaving.  Neighbouring sensor pixels share grid cells (8 rays per cell
+// along x at 2048^2 rays / 256^3 voxels), so with ray i on lane i the lanes of a
+// warp splat into the same few addresses and every RED is replayed once per
+// colliding lane.  Instead of repairing that with shuffles, the adjoint assigns
+// rays to lanes with a stride: with interleave IL = 2^sh, IL consecutive warps
+// share a tile of 32*IL consecutive rays and lane l of warp w takes ray
+// tile*32*IL + l*IL + w.  The lanes of one warp then sit in 32 DIFFERENT,
+// x-adjacent cells: gathers and REDs of a warp cover consecutive addresses (full
+// sectors, no same-address collisions), at no instruction cost.  IL is measured
+// on the device from the batch itself (average number of consecutive rays per
+// cell in a sample), so no host synchronisation is needed.
+// ---------------------------------------------------------------------------
+constexpr int kInterleaveSlots = 64;
+constexpr int kInterleaveMax = 32;
+__device__ int g_interleave_log2[kInterleaveSlots];
+
+__global__ void __launch_bounds__(256) estimate_interleave_kernel(GridP g, const float *pos, int64_t N,
+                                                                  int layout, int forced_log2, int *out) {
+  if (forced_log2 >= 0) {
+    if (threadIdx.x == 0) *out = forced_log2;
+    return;
+  }
+  __shared__ int s_breaks;
+  if (threadIdx.x == 0) s_breaks = 0;
+  __syncthreads();
+  const int S = (int) (N < 8192 ? N : 8192);
+  const int64_t start = (N - S) / 2;
+  int breaks = 0;
+  for (int i = threadIdx.x + 1; i < S; i += blockDim.x) {
+    CellIdx a = cell_of(g, ld3(pos, start + i - 1, N, layout)), b = cell_of(g, ld3(pos, start + i, N, layout));
+    breaks += (a.fx != b.fx) | (a.fy != b.fy) | (a.fz != b.fz);
+  }
+  breaks = __reduce_add_sync(kFull, breaks);
+  if ((threadIdx.x & 31) == 0) atomicAdd(&s_breaks, breaks);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const float m = (float) S / (float) (s_breaks + 1);  // average consecutive rays per cell
+    int sh = 0;
+    while ((2 << sh) <= kInterleaveMax && (float) (2 << sh) <= 1.1f * m) ++sh;
+    *out = sh;
+  }
 }
 
 template <bool SDF, int AR, class Accum, bool AGG>
@@ -316,8 +395,13 @@ __global__ void __launch_bounds__(kAdjThreads) backtrace_kernel(AdjArgs a, Accum
   constexpr bool TRAJ_REF = AR != A_FAST;
   Accum out = out_in;
   out.prepare();
-  const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned lane = threadIdx.x & 31;
+  int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (a.interleave_log2) {  // see "Ray interleaving" above
+    const int sh = *a.interleave_log2;
+    const int64_t gw = r >> 5;
+    r = ((((gw >> sh) << 5) + lane) << sh) | (gw & ((1 << sh) - 1));
+  }
   const bool valid = r < a.N;
   int steps = 0;  // per ray < max_steps < 2^31
   const GridP g = a.grid;
@@ -343,6 +427,7 @@ __global__ void __launch_bounds__(kAdjThreads) backtrace_kernel(AdjArgs a, Accum
   }
   CellAddr ca = {0, 0, 0, 0};
   f32x2 P[4] = {0ull, 0ull, 0ull, 0ull};  // accumulator pairs (acc[2j], acc[2j+1])
+  AggState agg = {1, 0};
   bool have = false;
   for (int i = 0; i < a.max_steps; ++i) {
     if (AGG) {
@@ -360,7 +445,7 @@ __global__ void __launch_bounds__(kAdjThreads) backtrace_kernel(AdjArgs a, Accum
     if (!REF) {
       const bool fl = have && (chg || !active);
       if (AGG) {
-        flush_aggregated(out, ca, P, fl, lane);
+        flush_aggregated(out, ca, P, fl, lane, a.agg_policy, agg);
       } else if (fl) {
         float acc[8];
         unpack8(P, acc);
@@ -423,7 +508,7 @@ __global__ void __launch_bounds__(kAdjThreads) backtrace_kernel(AdjArgs a, Accum
   }
   if (!REF) {
     if (AGG) {
-      flush_aggregated(out, ca, P, have, lane);
+      flush_aggregated(out, ca, P, have, lane, a.agg_policy, agg);
     } else if (have) {
       float acc[8];
       unpack8(P, acc);
@@ -465,15 +550,34 @@ int launch_trace(int kind, int arith, const TraceArgs &a, cudaStream_t s) {
 
 template <bool SDF, class Accum, bool AGG>
 static void launch_backtrace_acc(int arith, const AdjArgs &a, Accum acc, cudaStream_t s) {
-  unsigned nb = blocks_for(a.N, kAdjThreads);
+  // with interleaving the thread count is rounded up to whole tiles of the largest interleave
+  const int64_t tile = 32 * kInterleaveMax;
+  const int64_t nthreads = a.interleave_log2 ? ((a.N + tile - 1) / tile) * tile : a.N;
+  unsigned nb = blocks_for(nthreads, kAdjThreads);
   if (arith == A_REF) backtrace_kernel<SDF, A_REF, Accum, false><<<nb, kAdjThreads, 0, s>>>(a, acc);
   else if (arith == A_FAST) backtrace_kernel<SDF, A_FAST, Accum, AGG><<<nb, kAdjThreads, 0, s>>>(a, acc);
   else backtrace_kernel<SDF, A_EXACT, Accum, AGG><<<nb, kAdjThreads, 0, s>>>(a, acc);
 }
 
-int launch_backtrace(bool sdf, int arith, bool warp_agg, const AdjArgs &a, float *grad,
+int launch_backtrace(bool sdf, int arith, bool warp_agg, int interleave, const AdjArgs &a_in, float *grad,
                      unsigned long long *fixed, const unsigned *fixed_max_bits, cudaStream_t s) {
-  if (a.N <= 0) return 0;
+  if (a_in.N <= 0) return 0;
+  AdjArgs a = a_in;
+  int launched = 1;
+  a.interleave_log2 = nullptr;
+  // interleave: 0 = off, -1 = measured on the device, 2^k = forced
+  if (interleave != 0 && a.N >= 4096) {
+    static std::atomic<unsigned> next_slot{0};
+    int *slots = nullptr;
+    if (cudaGetSymbolAddress((void **) &slots, g_interleave_log2) == cudaSuccess) {
+      int *slot = slots + (next_slot++ % kInterleaveSlots);
+      int forced = -1;
+      if (interleave > 0) { forced = 0; while ((2 << forced) <= interleave && (2 << forced) <= kInterleaveMax) ++forced; }
+      estimate_interleave_kernel<<<1, 256, 0, s>>>(a.grid, a.xt, a.N, a.layout, forced, slot);
+      a.interleave_log2 = slot;
+      ++launched;
+    }
+  }
   if (fixed) {
     // integer accumulation must not depend on how lanes are grouped: no float pre-summation
     AccumFixed acc{fixed, fixed_max_bits, 1.0f};
@@ -489,7 +593,7 @@ int launch_backtrace(bool sdf, int arith, bool warp_agg, const AdjArgs &a, float
       else launch_backtrace_acc<false, AccumFloat, false>(arith, a, acc, s);
     }
   }
-  return 1;
+  return launched;
 }
 
 }  // namespace drrt

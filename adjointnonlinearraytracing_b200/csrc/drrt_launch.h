@@ -41,6 +41,8 @@ struct AdjArgs {
   int layout;
   float ds;
   int max_steps;
+  int agg_policy;  // warp aggregation: 0 adaptive, 2/4/8 fixed maximum run length
+  const int *interleave_log2;  // device: log2 of the ray interleave, or NULL (identity mapping)
   int64_t *stats;
 };
 
@@ -59,7 +61,8 @@ struct CableArgs {
 // kind: 0 plain, 1 plane, 2 target, 3 sdf.  Returns the number of kernels launched.
 // arith: 0 fast polynomial, 1 reference-literal, 2 exact-trajectory (default)
 int launch_trace(int kind, int arith, const TraceArgs &a, cudaStream_t s);
-int launch_backtrace(bool sdf, int arith, bool warp_agg, const AdjArgs &a, float *grad,
+// interleave: 0 off, -1 measured on the device, 2^k forced
+int launch_backtrace(bool sdf, int arith, bool warp_agg, int interleave, const AdjArgs &a, float *grad,
                      unsigned long long *fixed, const unsigned *fixed_max_bits, cudaStream_t s);
 int launch_trace_cable(bool ref_arith, const CableArgs &a, cudaStream_t s);
 int launch_backtrace_cable(bool ref_arith, const CableArgs &a, float *grad,

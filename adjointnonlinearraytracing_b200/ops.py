@@ -18,8 +18,8 @@ from typing import Optional, Sequence, Tuple
 import torch
 
 from . import _capi
-from ._capi import (DRRT_ACCUMULATE, DRRT_AOS, DRRT_DETERMINISTIC, DRRT_FAST_ARITH,
-                    DRRT_NO_WARP_AGGREGATION, DRRT_REFERENCE_ARITH, DRRT_SOA)
+from ._capi import (DRRT_ACCUMULATE, DRRT_AOS, DRRT_DETERMINISTIC, DRRT_FAST_ARITH, DRRT_INTERLEAVE,
+                    DRRT_NO_INTERLEAVE, DRRT_REFERENCE_ARITH, DRRT_SOA, DRRT_WARP_AGGREGATION)
 
 __all__ = [
     "trace", "trace_pln", "trace_target", "trace_sdf", "trace_cable", "backtrace",
@@ -30,15 +30,17 @@ __all__ = [
 
 def make_flags(reference_arith: bool = False, deterministic: bool = False,
                accumulate: bool = False, fast_arith: bool = False,
-               warp_aggregation: bool = True) -> int:
-    """Flag word of the C ABI (include/drrt_b200.h).  Default arithmetic = exact trajectory."""
+               warp_aggregation: bool = False, interleave=None) -> int:
+    """Flag word of the C ABI (include/drrt_b200.h).  Default arithmetic = exact trajectory;
+    `interleave`: None = measured on the device, 0/False = off, 2^k = forced."""
     if reference_arith and fast_arith:
         raise ValueError("reference_arith and fast_arith are mutually exclusive")
     return ((DRRT_REFERENCE_ARITH if reference_arith else 0)
             | (DRRT_DETERMINISTIC if deterministic else 0)
             | (DRRT_ACCUMULATE if accumulate else 0)
             | (DRRT_FAST_ARITH if fast_arith else 0)
-            | (0 if warp_aggregation else DRRT_NO_WARP_AGGREGATION))
+            | (DRRT_WARP_AGGREGATION if warp_aggregation else 0)
+            | (0 if interleave is None else DRRT_NO_INTERLEAVE if not interleave else DRRT_INTERLEAVE(interleave)))
 
 
 def new_stats(device) -> torch.Tensor:

@@ -67,17 +67,30 @@ enum {
    * few rays per 10^4 take the other branch at a cell face. */
   DRRT_REFERENCE_ARITH = 1u << 0,
   DRRT_FAST_ARITH = 1u << 3,
-  /* Adjoint only: issue every lane's atomics itself instead of pre-summing lanes
-   * that hit the same cell (A/B switch for profiling). */
-  DRRT_NO_WARP_AGGREGATION = 1u << 4,
+  /* Adjoint only, A/B switches for profiling (defaults: interleave measured on the
+   * device, no warp aggregation).
+   * DRRT_NO_INTERLEAVE: ray i on thread i instead of the strided assignment that puts
+   * the lanes of a warp into different cells.
+   * DRRT_WARP_AGGREGATION: pre-sum lanes that flush the same cell with a segmented
+   * shuffle reduction before the atomics (the alternative to interleaving).
+   * bits 8-11  DRRT_AGG_RUN(n), n in {2,4,8}: fixed maximum run length for the
+   *            aggregation; 0 = adaptive.
+   * bits 12-17 DRRT_INTERLEAVE(n), n in {1,2,4,8,16,32}: fixed interleave; 0 = measured. */
+  DRRT_NO_WARP_AGGREGATION = 0u, /* kept for source compatibility: aggregation is opt-in */
+  DRRT_WARP_AGGREGATION = 1u << 4,
+  DRRT_NO_INTERLEAVE = 1u << 5,
   /* Adjoint only: accumulate the gradient in 64-bit fixed point so the result is
-   * bit-stable from run to run regardless of atomic ordering. */
+   * bit-stable from run to run regardless of atomic ordering (and of the ray
+   * order / interleave). */
   DRRT_DETERMINISTIC = 1u << 1,
   /* Adjoint only: do NOT zero-fill `grad` first (the reference always returns a
    * fresh grid, src/tracer.cpp:401-403; set this to accumulate several ray
    * batches into one grid). */
   DRRT_ACCUMULATE = 1u << 2
 };
+
+#define DRRT_AGG_RUN(n) ((unsigned) (n) << 8)
+#define DRRT_INTERLEAVE(n) ((unsigned) (n) << 12)
 
 int drrt_abi_version(void);
 const char *drrt_last_error(void);

@@ -26,7 +26,8 @@ pytestmark = pytest.mark.gpu
 REF = 1  # DRRT_REFERENCE_ARITH
 DET = 2  # DRRT_DETERMINISTIC
 FAST = 8  # DRRT_FAST_ARITH
-NOAGG = 16  # DRRT_NO_WARP_AGGREGATION
+AGG = 16  # DRRT_WARP_AGGREGATION
+NOIL = 32  # DRRT_NO_INTERLEAVE
 
 
 @pytest.fixture(scope="module")
@@ -64,7 +65,7 @@ def test_golden_trace_backtrace(case, golden, ops, oracle_mod):
     # default flags: exact-trajectory arithmetic
     xd, vd = ops.trace(T(g["rif"]), T(g["pos"]), T(g["vel"]), g["h"], g["ds"])
     assert np.array_equal(N(xd), xp) and np.array_equal(N(vd), vp)
-    for fl in (0, NOAGG, DET):
+    for fl in (0, AGG, NOIL, AGG | NOIL, DET):
         gd = ops.backtrace(T(g["rif"]), T(g["xt"]), T(g["vt"]), T(g["dx"]), T(g["dv"]), g["h"], g["ds"], flags=fl)
         assert rel_l2(N(gd), gp) <= 1e-5, (fl, rel_l2(N(gd), gp))
         assert rel_l2(N(gd), g["grad"]) <= 1e-4
@@ -165,7 +166,7 @@ def test_seeded_vs_restatement(ng, s, field, ops, oracle_mod):
     st = ops.new_stats("cuda")
     xd, vd = ops.trace(T(rif), T(pos), T(vel), h, ds, stats=st)
     assert np.array_equal(N(xd), xp) and np.array_equal(N(vd), vp) and int(st[0]) == steps_f
-    for fl in (0, NOAGG, DET):
+    for fl in (0, AGG, NOIL, AGG | NOIL, DET):
         st = ops.new_stats("cuda")
         gd = ops.backtrace(T(rif), T(xp), T(vp), T(dx), T(dv), h, ds, flags=fl, stats=st)
         assert int(st[0]) == steps_b
@@ -200,7 +201,7 @@ def test_noncubic_and_ragged(ops, oracle_mod):
     gp = oracle_mod.port.backtrace(rif, xp, vp, dx, dv, h, ds, res=(W, H, D))
     xd, vd = ops.trace(T(rif), T(pos), T(vel), h, ds, res=(W, H, D))
     assert np.array_equal(N(xd), xp) and np.array_equal(N(vd), vp)
-    for fl in (REF, REF | DET, 0, DET, NOAGG, FAST, FAST | DET):
+    for fl in (REF, REF | DET, 0, DET, AGG, NOIL, FAST, FAST | DET):
         gg = ops.backtrace(T(rif), T(xp), T(vp), T(dx), T(dv), h, ds, res=(W, H, D), flags=fl)
         assert rel_l2(N(gg), gp) <= (2e-6 if fl & REF else 5e-3 if fl & FAST else 1e-5), (fl, rel_l2(N(gg), gp))
 

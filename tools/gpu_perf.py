@@ -17,7 +17,7 @@ from adjointnonlinearraytracing_b200 import ops, scenes as sc  # noqa: E402
 
 dev = torch.device("cuda:0")
 T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
-REF, DET, FAST, NOAGG = 1, 2, 8, 16
+REF, DET, FAST, AGG, NOIL = 1, 2, 8, 16, 32
 
 
 def timeit(fn, iters=5):
@@ -44,8 +44,8 @@ def main():
         dx = torch.ones_like(pos); dv = torch.ones_like(pos)
         xr, vr = ops.trace(rif, pos, vel, h, ds, flags=REF)
         gref = ops.backtrace(rif, xr, vr, dx, dv, h, ds, flags=REF)
-        for nm, fl in [("exact", 0), ("exact-noagg", NOAGG), ("fast", FAST), ("fast-noagg", FAST | NOAGG),
-                       ("ref", REF), ("exact-det", DET)]:
+        for nm, fl in [("exact", 0), ("exact-noil", NOIL), ("exact-agg-noil", AGG | NOIL), ("fast", FAST),
+                       ("ref", REF), ("exact-det", DET), ("exact-det-noil", DET | NOIL)]:
             st = ops.new_stats(dev)
             xt, vt = ops.trace(rif, pos, vel, h, ds, flags=fl, stats=st); sf = int(st[0])
             tf = timeit(lambda: ops.trace(rif, pos, vel, h, ds, flags=fl))
@@ -53,7 +53,7 @@ def main():
             g = ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=fl, stats=st); sb = int(st[0])
             tb = timeit(lambda: ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=fl))
             same = bool(torch.equal(xt, xr) and torch.equal(vt, vr))
-            print(f"{Ng}^3 {S}^2 {kind:10s} {nm:12s} fwd {sf/tf/1e6:6.1f} G/s ({tf:6.2f} ms) adj {sb/tb/1e6:6.1f} G/s ({tb:6.2f} ms) "
+            print(f"{Ng}^3 {S}^2 {kind:10s} {nm:15s} fwd {sf/tf/1e6:6.1f} G/s ({tf:6.2f} ms) adj {sb/tb/1e6:6.1f} G/s ({tb:6.2f} ms) "
                   f"both {(sf+sb)/(tf+tb)/1e6:6.1f} G/s alg {(32*sf+64*sb)/(tf+tb)/1e6:5.0f} GB/s | endpoints==ref {same} "
                   f"grad relL2 vs ref {rel_l2(g, gref):.2e}", flush=True)
 
