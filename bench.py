@@ -31,6 +31,8 @@ SENSOR = 2048
 METRIC = "fwd+adjoint ray-steps/sec at 256^3 grid"
 UNIT = "ray-steps/s"
 BYTES_FWD, BYTES_ADJ = 32, 64  # algorithmic bytes per ray-step, SURVEY.md section 8d
+WORKLOAD = (f"caustic-256 (BASELINE.json configs[3]): {NG}^3 bump IOR grid, {SENSOR}^2 = {SENSOR * SENSOR} "
+            "collimated rays per GPU, ds = h/2, seeds dx=dv=1")
 
 
 def peaks():
@@ -190,12 +192,13 @@ def run_reference_arm(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"caustic-256: {NG}^3 bump grid, {SENSOR}^2 collimated rays, ds=h/2 (CPU: bounded sample)"},
+        "config": {"workload": WORKLOAD, "rays_per_gpu": SENSOR * SENSOR, "grid": [NG, NG, NG],
+                   "note": "CPU reference arm: each step is a bounded strided sample of the batch (cpu_baseline.sample)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": arm.threads, "kind": arm.kind, "sample": arm.describe()},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 # --------------------------------------------------------------------------- GPU arm
@@ -345,7 +348,7 @@ def run_ours(args):
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {
-                "workload": f"caustic-256 (BASELINE.json configs[3]): {NG}^3 bump IOR grid, {SENSOR}^2 = {n_rays} collimated rays per GPU, ds = h/2, seeds dx=dv=1",
+                "workload": WORKLOAD,
                 "rays_per_gpu": n_rays, "grid": [NG, NG, NG], "parallelism": f"rays-dp{world} + grad allreduce" if world > 1 else "single GPU",
                 "l2": "no explicit flush: per-step working set (rays in/out 302 MB + grid 67 MB + gradient 67 MB) exceeds the 126 MB L2; the 67 MB IOR grid staying L2-resident across the step is the design",
                 "arithmetic": "exact trajectory (default flags=0): ray path bit-identical to the float32 reference formulas", "ray_steps_fwd": s_f, "ray_steps_adj": s_b,
@@ -374,11 +377,31 @@ def run_ours(args):
             t = arm.step()
             line["cpu_baseline"] = {"value": (sf + sb) / t, "unit": UNIT, "cores": arm.threads, "kind": arm.kind,
                                     "sample": arm.describe(), "seconds": t}
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if allreduce is not None:
         allreduce.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+_REAL_STDOUT = None
+
+
+def _guard_stdout():
+    """Everything libraries print to fd 1 (e.g. NCCL's version banner) goes to stderr; the one JSON
+    line is written to the original stdout by _emit()."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def _emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
@@ -389,6 +412,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
+    _guard_stdout()
     if args.impl == "reference":
         run_reference_arm(args)
     else:
