@@ -135,7 +135,7 @@ __device__ __forceinline__ float dist2_ref(f3 x, f3 t) {
 // trace_target (:174-242, per-ray part), trace_sdf (:244-310).
 // ---------------------------------------------------------------------------
 template <int KIND, int AR>
-__global__ void __launch_bounds__(kTraceThreads) trace_kernel(TraceArgs a) {
+__global__ void __launch_bounds__(kTraceThreads, KIND == K_PLAIN ? kTraceMinBlocks : 8) trace_kernel(TraceArgs a) {
   constexpr bool REF = AR != A_FAST;
   const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
   const bool valid = r < a.N;
@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(kTraceThreads) trace_kernel(TraceArgs a) {
     GridP sg = g;
     sg.data = a.sdf;
     int i = 0;
-    for (; i < a.max_steps; ++i) {
+    if (a.max_steps > 0) do {  // single exit test at the bottom: !esc && i < max_steps
       if (inside) {  // masked gather: outside lanes see n = 0, grad n = 0 and fly straight
         CellIdx c = cell_of(g, x);
         if (cc.differs(c)) cc.refill(g, c);
@@ -179,17 +179,23 @@ __global__ void __launch_bounds__(kTraceThreads) trace_kernel(TraceArgs a) {
       if (KIND == K_SDF) {  // :287-288, evaluated under the previous `inside`
         cur_inside = inside ? (eval_value<AR>(sg, sc, x) < 0.f) : false;
       }
-      const bool cross = inside & !cur_inside;  // :74
       if (KIND == K_TARGET) {  // :216-227
         float cur = dist2_ref(x, aux0);
         if (cur < best) { xt = x; vt = v; best = cur; }
       }
-      esc = cross | (!inb && escaped(g, x, v));  // :75-76 (escaped() implies !inbounds)
-      inside = cur_inside;  // :86
-      // :79-80 capture: a crossing always ends the ray's loop, so (x, v) at the break
-      // ARE the captured exit state; the copy is done once after the loop.
-      if (esc) { crossed = cross; ++i; break; }
-    }
+      // :74-76.  Nothing can end the ray while it stays inside (cross needs !cur_inside,
+      // escaped() implies !inbounds), so the exit logic sits behind one rarely taken branch.
+      ++i;
+      if (cur_inside & inb) {
+        inside = true;  // :86 (fast path: still inside, nothing can end the ray)
+      } else {
+        crossed = inside & !cur_inside;
+        // :79-80 capture: a crossing always ends the ray's loop, so (x, v) at loop exit
+        // ARE the captured exit state; the copy is done once after the loop.
+        esc = crossed | (!inb && escaped(g, x, v));
+        inside = cur_inside;  // :86
+      }
+    } while (!esc && i < a.max_steps);
     steps = i;
     if (KIND != K_TARGET && crossed) { xt = x; vt = v; }
     if (!esc) {
@@ -390,7 +396,7 @@ __global__ void __launch_bounds__(256) estimate_interleave_kernel(GridP g, const
 }
 
 template <bool SDF, int AR, class Accum, bool AGG>
-__global__ void __launch_bounds__(kAdjThreads) backtrace_kernel(AdjArgs a, Accum out_in) {
+__global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF) ? 5 : kAdjMinBlocks) backtrace_kernel(AdjArgs a, Accum out_in) {
   constexpr bool REF = AR == A_REF;     // literal 16-atomic splat and lambda/mu order
   constexpr bool TRAJ_REF = AR != A_FAST;
   Accum out = out_in;

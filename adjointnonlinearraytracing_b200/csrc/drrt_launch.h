@@ -14,6 +14,14 @@ namespace drrt {
 
 constexpr int kTraceThreads = 128;
 constexpr int kAdjThreads = 128;
+#ifndef DRRT_ADJ_MIN_BLOCKS
+#define DRRT_ADJ_MIN_BLOCKS 7
+#endif
+#ifndef DRRT_TRACE_MIN_BLOCKS
+#define DRRT_TRACE_MIN_BLOCKS 9
+#endif
+constexpr int kAdjMinBlocks = DRRT_ADJ_MIN_BLOCKS;
+constexpr int kTraceMinBlocks = DRRT_TRACE_MIN_BLOCKS;
 
 struct TraceArgs {
   GridP grid;
