@@ -448,6 +448,10 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF) ? 5 : kAdjMi
       c = cell_of(g, x);
       chg = cc.differs(c);
     }
+    // the new cell's gather is issued BEFORE the old cell's accumulators are flushed, so the
+    // L2 latency of the face the ray moves towards overlaps the address arithmetic and REDs
+    CellAddr nca = ca;
+    if (chg) nca = cc.refill(g, c);
     if (!REF) {
       const bool fl = have && (chg || !active);
       if (AGG) {
@@ -462,8 +466,8 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF) ? 5 : kAdjMi
         have = false;
       }
     }
+    ca = nca;
     if (active) {
-      if (chg) ca = cc.refill(g, c);
       float n; f3 nx, hm;
       cc.eval(g, c, n, nx, &hm);  // :421-422 (same 8 voxels serve grad and Hessian)
       float mdsn = TRAJ_REF ? mul_(-ds, n) : -ds * n;
