@@ -50,6 +50,8 @@ PROTOTYPES = {
     "drrt_volume_splat": (c_int, [_P, _I, _I, _I, _P, _P, _P, _L, _I, _F, _P]),
     "drrt_cylinder_eval": (c_int, [_P, _I, _F, _F, _P, _L, _I, _P, _P, _P, _P]),
     "drrt_cylinder_splat": (c_int, [_P, _I, _F, _F, _P, _P, _P, _L, _I, _P]),
+    "drrt_adam_step": (c_int, [_P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _F, _F, _F, _U, _P]),
+    "drrt_upres_volume": (c_int, [_P, _I, _I, _I, _P, _I, _I, _I, _P]),
     "drrt_trace_host": (c_int, [_P, _I, _I, _I, _P, _P, _L, _I, _F, _F, _P, _P, _P, _U]),
     "drrt_backtrace_host": (c_int, [_P, _I, _I, _I, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, _U]),
     "drrt_host_cache_grid": (None, [_I]),

@@ -294,6 +294,28 @@ int drrt_backtrace_cable(const float *rif, int res, float radius, float length, 
   return check_launch("backtrace_cable");
 }
 
+int drrt_adam_step(float *n, const float *grad, float *exp_avg, float *exp_avg_sq, int S0, int S1, int S2,
+                   int step, float lr, float beta1, float beta2, float eps, float clamp_min,
+                   unsigned flags, drrt_stream_t stream) {
+  if (S0 <= 0 || S1 <= 0 || S2 <= 0) return fail(DRRT_ERR_RESOLUTION, "Resolution doesn't match data");
+  if (!n || !grad || !exp_avg || !exp_avg_sq) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL grid buffer");
+  if (step < 1) return fail(DRRT_ERR_INVALID_ARGUMENT, "step counts from 1 (torch.optim.Adam)");
+  int r = launch_adam_step(n, grad, exp_avg, exp_avg_sq, S0, S1, S2, step, lr, beta1, beta2, eps, clamp_min,
+                           !(flags & DRRT_ADAM_KEEP_BOUNDARY), !(flags & DRRT_ADAM_NO_CLAMP), (cudaStream_t) stream);
+  if (r < 0) return fail(DRRT_ERR_RESOLUTION, "grid too large for one launch");
+  g_launches += r;
+  return check_launch("adam_step");
+}
+
+int drrt_upres_volume(const float *src, int s0, int s1, int s2, float *dst, int d0, int d1, int d2,
+                      drrt_stream_t stream) {
+  if (s0 <= 0 || s1 <= 0 || s2 <= 0 || d0 <= 0 || d1 <= 0 || d2 <= 0)
+    return fail(DRRT_ERR_RESOLUTION, "Resolution doesn't match data");
+  if (!src || !dst) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL grid buffer");
+  g_launches += launch_upres_volume(src, s0, s1, s2, dst, d0, d1, d2, (cudaStream_t) stream);
+  return check_launch("upres_volume");
+}
+
 int drrt_volume_eval(const float *rif, int W, int H, int D, const float *pos, int64_t N,
                      int layout, float h, float *n, float *grad, float *hess, unsigned flags,
                      drrt_stream_t stream) {

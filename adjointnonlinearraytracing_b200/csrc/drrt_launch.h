@@ -83,6 +83,13 @@ int launch_fixed_max(const float *dx, const float *dv, int64_t n3, unsigned *max
 int launch_fixed_to_float(const unsigned long long *fixed, const unsigned *max_bits, float *grad,
                           int64_t G, bool accumulate, cudaStream_t s);
 
+// optimiser step / up-res
+int launch_adam_step(float *n, const float *grad, float *m, float *v, int S0, int S1, int S2, int step,
+                     float lr, float beta1, float beta2, float eps, float clamp_min, bool zero_boundary,
+                     bool clamp, cudaStream_t s);
+int launch_upres_volume(const float *src, int s0, int s1, int s2, float *dst, int d0, int d1, int d2,
+                        cudaStream_t s);
+
 // volume probes
 int launch_volume_eval(const GridP &g, const float *pos, int64_t N, int layout, float *n,
                        float *grad, float *hess, bool ref_arith, cudaStream_t s);

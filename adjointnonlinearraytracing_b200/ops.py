@@ -314,3 +314,37 @@ def cylinder_splat(data, radius, length, pos, val, grad):
                                                      _ptr(pos), _ptr(val), _ptr(grad), N, DRRT_AOS,
                                                      _stream(data)))
     return data
+
+
+# --------------------------------------------------------------------------- optimiser step
+def adam_step_(n, grad, exp_avg, exp_avg_sq, step, lr, betas=(0.9, 0.999), eps=1e-8, clamp_min=1.0,
+               zero_boundary=True, clamp=True):
+    """One fused pass = ``n.grad[boundary] = 0; torch.optim.Adam.step(); n.clamp_(min=clamp_min)``
+    (reference core/optimizer.py:61-68).  Updates ``n``, ``exp_avg``, ``exp_avg_sq`` in place."""
+    for name, t in (("n", n), ("grad", grad), ("exp_avg", exp_avg), ("exp_avg_sq", exp_avg_sq)):
+        if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise RuntimeError(f"{name}: expected a contiguous float32 CUDA tensor")
+        if t.shape != n.shape:
+            raise RuntimeError("Resolution doesn't match data")
+    if n.dim() != 3:
+        raise RuntimeError("adam_step_: expected a 3-D grid")
+    S0, S1, S2 = (int(s) for s in n.shape)
+    flags = (0 if zero_boundary else 1) | (0 if clamp else 2)
+    with torch.cuda.device(n.device):
+        _capi.check(_capi.load().drrt_adam_step(_ptr(n), _ptr(grad), _ptr(exp_avg), _ptr(exp_avg_sq), S0, S1, S2,
+                                                int(step), float(lr), float(betas[0]), float(betas[1]), float(eps),
+                                                float(clamp_min), flags, _stream(n)))
+    return n
+
+
+def upres_volume(n, new_res):
+    """``grid.upres_volume`` / ``optimizer.upres_scene`` (reference core/grid.py:318-330,
+    core/optimizer.py:7-10): trilinear resample of a cubic grid to ``new_res``."""
+    src = _dev(n, "n")
+    if src.dim() != 3:
+        raise RuntimeError("upres_volume: expected a 3-D grid")
+    d = [int(r) for r in new_res]
+    dst = torch.empty(d, dtype=torch.float32, device=src.device)
+    with torch.cuda.device(src.device):
+        _capi.check(_capi.load().drrt_upres_volume(_ptr(src), *(int(s) for s in src.shape), _ptr(dst), *d, _stream(src)))
+    return dst

@@ -171,6 +171,22 @@ int drrt_cylinder_splat(float *data, int res, float radius, float length, const 
                         const float *val, const float *grad, int64_t N, int layout,
                         drrt_stream_t stream);
 
+/* ---- optimiser step and multires up-res (the callers' side of the adjoint) -----
+ * drrt_adam_step    <- one iteration of the loop body of multires_opt, reference
+ *                      core/optimizer.py:61-68, fused into one pass over the grid:
+ *                      n.grad[boundary] = 0 (mask = everything but [1:-1,1:-1,1:-1]),
+ *                      torch.optim.Adam step (no weight decay / amsgrad; `step` counts
+ *                      from 1), n.clamp_(min = clamp_min).  (S0,S1,S2) = n.shape.
+ * drrt_upres_volume <- upres_scene / grid.upres_volume (core/optimizer.py:7-10,
+ *                      core/grid.py:318-330): trilinear resample on linspace(0,1)
+ *                      lattices, evaluated in float64 like the reference. */
+enum { DRRT_ADAM_KEEP_BOUNDARY = 1u << 0, DRRT_ADAM_NO_CLAMP = 1u << 1 };
+int drrt_adam_step(float *n, const float *grad, float *exp_avg, float *exp_avg_sq, int S0, int S1, int S2,
+                   int step, float lr, float beta1, float beta2, float eps, float clamp_min,
+                   unsigned flags, drrt_stream_t stream);
+int drrt_upres_volume(const float *src, int s0, int s1, int s2, float *dst, int d0, int d1, int d2,
+                      drrt_stream_t stream);
+
 /* ---- host-buffer entry points (what a non-torch binding of the reference API
  * calls; device memory is managed inside the library and cached per thread) --- */
 int drrt_trace_host(const float *rif, int W, int H, int D, const float *pos, const float *vel,
