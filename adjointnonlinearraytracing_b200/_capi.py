@@ -46,6 +46,7 @@ PROTOTYPES = {
     "drrt_backtrace": (c_int, [_P, _I, _I, _I, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, _P, _U, _P]),
     "drrt_backtrace_sdf": (c_int, [_P, _P, _I, _I, _I, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, _P, _U, _P]),
     "drrt_backtrace_cable": (c_int, [_P, _I, _F, _F, _P, _P, _P, _P, _L, _I, _F, _P, _P, _P, _U, _P]),
+    "drrt_backtrace_rays": (c_int, [_P, _P, _I, _I, _I, _P, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, _P, _P, _P, _U, _P]),
     "drrt_volume_eval": (c_int, [_P, _I, _I, _I, _P, _L, _I, _F, _P, _P, _P, _U, _P]),
     "drrt_volume_splat": (c_int, [_P, _I, _I, _I, _P, _P, _P, _L, _I, _F, _P]),
     "drrt_cylinder_eval": (c_int, [_P, _I, _F, _F, _P, _L, _I, _P, _P, _P, _P]),

@@ -147,9 +147,11 @@ int trace_common(int kind, const float *rif, const float *sdf, int W, int H, int
 int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, int H, int D,
                      const float *xt, const float *vt, const float *dx, const float *dv, int64_t N,
                      int layout, float h, float ds, float *grad, void *scratch, int64_t *stats,
-                     unsigned flags, cudaStream_t s) {
+                     unsigned flags, cudaStream_t s, const float *pos0 = nullptr, float *dpos = nullptr,
+                     float *dvel = nullptr) {
   AdjArgs a;
   memset(&a, 0, sizeof a);
+  a.pos0 = pos0; a.dpos = dpos; a.dvel = dvel;
   int rc = make_grid(a.grid, rif, W, H, D, h);
   if (rc) return rc;
   if ((rc = check_rays(N, layout, ds))) return rc;
@@ -259,6 +261,15 @@ int drrt_backtrace_sdf(const float *rif, const float *sdf, int W, int H, int D, 
   if (!sdf) return fail(DRRT_ERR_INVALID_ARGUMENT, "sdf is NULL");
   return backtrace_common(true, rif, sdf, W, H, D, xt, vt, dx, dv, N, layout, h, ds, grad, scratch,
                           stats, flags, (cudaStream_t) stream);
+}
+
+int drrt_backtrace_rays(const float *rif, const float *sdf, int W, int H, int D, const float *xt,
+                        const float *vt, const float *dx, const float *dv, const float *pos0, int64_t N,
+                        int layout, float h, float ds, float *grad, float *dpos, float *dvel,
+                        void *scratch, int64_t *stats, unsigned flags, drrt_stream_t stream) {
+  if (N > 0 && (!dpos || !dvel)) return fail(DRRT_ERR_INVALID_ARGUMENT, "dpos / dvel is NULL");
+  return backtrace_common(sdf != nullptr, rif, sdf, W, H, D, xt, vt, dx, dv, N, layout, h, ds, grad,
+                          scratch, stats, flags, (cudaStream_t) stream, pos0, dpos, dvel);
 }
 
 int drrt_backtrace_cable(const float *rif, int res, float radius, float length, const float *xt,

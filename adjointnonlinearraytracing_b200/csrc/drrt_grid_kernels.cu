@@ -395,8 +395,16 @@ __global__ void __launch_bounds__(256) estimate_interleave_kernel(GridP g, const
   }
 }
 
-template <bool SDF, int AR, class Accum, bool AGG>
-__global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF) ? 5 : kAdjMinBlocks) backtrace_kernel(AdjArgs a, Accum out_in) {
+// RG ("ray gradients"): also return dL/dpos and dL/dvel of the LAUNCH state.
+// With a_k = dL/dx_k, b_k = dL/dv_k the recursion below holds lambda = a_k and
+// mu = b_{k-1} after sample x_k has been processed; before x_k the forward ray flew
+// straight (gathers masked to zero outside the box, src/tracer.cpp:66-71), where
+// a is constant and b_{j-1} = b_j + ds a_j.  So dL/dpos = lambda and
+// dL/dvel = mu + (k - 1) ds lambda, with k the number of straight steps between the
+// launch position and the last processed sample (k = 0 when `pos0` is not given, which
+// is exact for rays launched on the first in-bounds sample).
+template <bool SDF, int AR, class Accum, bool AGG, bool RG = false>
+__global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : kAdjMinBlocks) backtrace_kernel(AdjArgs a, Accum out_in) {
   constexpr bool REF = AR == A_REF;     // literal 16-atomic splat and lambda/mu order
   constexpr bool TRAJ_REF = AR != A_FAST;
   Accum out = out_in;
@@ -420,8 +428,10 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF) ? 5 : kAdjMi
   GridP sg = g;
   sg.data = a.sdf;
   bool outside = false;
+  f3 xl = {0, 0, 0}, vl = {0, 0, 0};  // RG: (x_k, v_k) of the last sample that updated lambda/mu
   if (valid) {
     x = ld3(a.xt, r, a.N, a.layout); v = ld3(a.vt, r, a.N, a.layout);
+    xl = x; vl = v;
     la = ld3(a.dx, r, a.N, a.layout); mu = ld3(a.dv, r, a.N, a.layout);
     mu.x = add_(mu.x, mul_(ds, la.x)); mu.y = add_(mu.y, mul_(ds, la.y)); mu.z = add_(mu.z, mul_(ds, la.z));  // :410
     f3 nv = {-v.x, -v.y, -v.z};
@@ -513,6 +523,7 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF) ? 5 : kAdjMi
           la.z = fmaf(ds, fmaf(dn, nx.z, h2), la.z);
           mu.x = fmaf(ds, la.x, mu.x); mu.y = fmaf(ds, la.y, mu.y); mu.z = fmaf(ds, la.z, mu.z);
         }
+        if (RG) { xl = x; vl = v; }
       }
     }
   }
@@ -524,6 +535,19 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF) ? 5 : kAdjMi
       unpack8(P, acc);
       flush_direct(out, ca, acc);
     }
+  }
+  if (RG && valid) {
+    float k = 0.f;
+    if (a.pos0) {
+      const f3 x0 = ld3(a.pos0, r, a.N, a.layout);
+      const float num = (xl.x - x0.x) * vl.x + (xl.y - x0.y) * vl.y + (xl.z - x0.z) * vl.z;
+      const float den = ds * (vl.x * vl.x + vl.y * vl.y + vl.z * vl.z);
+      k = den > 0.f ? rintf(num / den) : 0.f;
+    }
+    const float t = (k - 1.f) * ds;
+    st3(a.dpos, r, a.N, a.layout, la);
+    f3 dv0 = {fmaf(t, la.x, mu.x), fmaf(t, la.y, mu.y), fmaf(t, la.z, mu.z)};
+    st3(a.dvel, r, a.N, a.layout, dv0);
   }
   if (a.stats) {
     const int64_t wsteps = warp_sum_i64((int64_t) steps);
@@ -564,6 +588,12 @@ static void launch_backtrace_acc(int arith, const AdjArgs &a, Accum acc, cudaStr
   const int64_t tile = 32 * kInterleaveMax;
   const int64_t nthreads = a.interleave_log2 ? ((a.N + tile - 1) / tile) * tile : a.N;
   unsigned nb = blocks_for(nthreads, kAdjThreads);
+  if (a.dpos) {  // ray gradients: no warp aggregation variant
+    if (arith == A_REF) backtrace_kernel<SDF, A_REF, Accum, false, true><<<nb, kAdjThreads, 0, s>>>(a, acc);
+    else if (arith == A_FAST) backtrace_kernel<SDF, A_FAST, Accum, false, true><<<nb, kAdjThreads, 0, s>>>(a, acc);
+    else backtrace_kernel<SDF, A_EXACT, Accum, false, true><<<nb, kAdjThreads, 0, s>>>(a, acc);
+    return;
+  }
   if (arith == A_REF) backtrace_kernel<SDF, A_REF, Accum, false><<<nb, kAdjThreads, 0, s>>>(a, acc);
   else if (arith == A_FAST) backtrace_kernel<SDF, A_FAST, Accum, AGG><<<nb, kAdjThreads, 0, s>>>(a, acc);
   else backtrace_kernel<SDF, A_EXACT, Accum, AGG><<<nb, kAdjThreads, 0, s>>>(a, acc);

@@ -52,6 +52,9 @@ struct AdjArgs {
   int agg_policy;  // warp aggregation: 0 adaptive, 2/4/8 fixed maximum run length
   const int *interleave_log2;  // device: log2 of the ray interleave, or NULL (identity mapping)
   int64_t *stats;
+  // ray gradients: dL/dpos, dL/dvel of the launch state; pos0 nullable
+  const float *pos0;
+  float *dpos, *dvel;
 };
 
 struct CableArgs {

@@ -23,7 +23,7 @@ from ._capi import (DRRT_ACCUMULATE, DRRT_AOS, DRRT_DETERMINISTIC, DRRT_FAST_ARI
 
 __all__ = [
     "trace", "trace_pln", "trace_target", "trace_sdf", "trace_cable", "backtrace",
-    "backtrace_sdf", "backtrace_cable", "volume_eval", "volume_splat", "cylinder_eval",
+    "backtrace_sdf", "backtrace_cable", "backtrace_rays", "volume_eval", "volume_splat", "cylinder_eval",
     "cylinder_splat", "make_flags", "new_stats",
 ]
 
@@ -244,6 +244,34 @@ def backtrace_sdf(rif, sdf, xt, vt, dx, dv, h, ds, *, res=None, flags=0, stats=N
                                                     float(ds), _ptr(grad), _ptr(scratch), _ptr(stats),
                                                     int(flags), _stream(rif)))
     return grad
+
+
+def backtrace_rays(rif, xt, vt, dx, dv, h, ds, *, pos0=None, sdf=None, res=None, flags=0, stats=None,
+                   out=None, layout="aos"):
+    """Adjoint pass that also returns the gradient w.r.t. the launch state, the contract of
+    ``ADTracerC.backward`` / ``ADSDFTracerC.backward`` (reference core/tracer.py:53-60):
+    -> (dL/d rif, dL/d pos, dL/d vel).  ``pos0`` = launch positions (recovers the number of
+    straight steps flown before the volume; omit for rays launched on the volume)."""
+    rif, (W, H, D) = _grid(rif, res)
+    if sdf is not None:
+        sdf, _ = _grid(sdf, (W, H, D), "sdf")
+    xt, N = _rays(xt, "xt", layout)
+    vt, _ = _rays(vt, "vt", layout, N)
+    dx, _ = _rays(dx, "dx", layout, N)
+    dv, _ = _rays(dv, "dv", layout, N)
+    if pos0 is not None:
+        pos0, _ = _rays(pos0, "pos0", layout, N)
+    dev = _same_device(rif, sdf, xt, vt, dx, dv, pos0, stats, out)
+    grad = _adj_out(out, rif, flags)
+    scratch = _scratch(rif.numel(), flags, dev)
+    dpos, dvel = torch.empty_like(xt), torch.empty_like(xt)
+    with torch.cuda.device(dev):
+        _capi.check(_capi.load().drrt_backtrace_rays(_ptr(rif), _ptr(sdf), W, H, D, _ptr(xt), _ptr(vt),
+                                                     _ptr(dx), _ptr(dv), _ptr(pos0), N, _lay(layout),
+                                                     float(h), float(ds), _ptr(grad), _ptr(dpos),
+                                                     _ptr(dvel), _ptr(scratch), _ptr(stats), int(flags),
+                                                     _stream(rif)))
+    return grad, dpos, dvel
 
 
 def backtrace_cable(rif, radius, length, xt, vt, dx, dv, ds, *, flags=0, stats=None, out=None,

@@ -5,7 +5,10 @@ reference's ``core/tracer.py``.
 ``core/tracer.py:294-526``).  The ``AD*`` classes of the reference differentiate the
 unrolled loop with enoki's tape (``core/tracer.py:16-291``); tape autodiff is the
 thing the adjoint replaces, so here they keep their call signature and route to
-the same adjoint kernels (gradient w.r.t. ``rif`` only, like ``Back*``).
+the same adjoint kernels.  ``ADTracerC`` and ``ADSDFTracerC`` also return
+dL/dx and dL/dv of the launch state like the reference (``core/tracer.py:53-60``),
+read off the adjoint's final co-state (``ops.backtrace_rays``); the plane, target and
+cable AD variants return the ``rif`` gradient only, like their ``Back*`` twins.
 
 Differences from the reference that a caller can observe: none in values beyond
 the stated float32 tolerances; ``ctx`` keeps torch tensors instead of enoki arrays
@@ -111,10 +114,56 @@ class BackCableTracerC(torch.autograd.Function):
         return drif.reshape(ctx.rif.shape), None, None, None, None, None, None
 
 
-# Tape-autodiff names of the reference (core/tracer.py:16-291): same signatures,
-# served by the adjoint.
-ADTracerC = BackTracerC
+class ADTracerC(torch.autograd.Function):
+    """reference core/tracer.py:16-68: gradients w.r.t. rif, x and v (each only when it
+    requires grad), served by the adjoint instead of enoki's tape."""
+
+    @staticmethod
+    def forward(ctx, rif, x, v, h, ds):
+        ctx.rif = rif.detach()
+        ctx.h, ctx.ds = h, ds
+        ctx.x0 = x.detach()
+        ctx.outx, ctx.outv = ops.trace(ctx.rif, x, v, h, ds, flags=FLAGS)
+        return ctx.outx, ctx.outv
+
+    @staticmethod
+    def backward(ctx, grad_x, grad_v):
+        need_rif, need_x, need_v = ctx.needs_input_grad[:3]
+        if not (need_x or need_v):
+            drif = ops.backtrace(ctx.rif, ctx.outx, ctx.outv, grad_x, grad_v, ctx.h, ctx.ds, flags=FLAGS)
+            return drif, None, None, None, None
+        drif, dx0, dv0 = ops.backtrace_rays(ctx.rif, ctx.outx, ctx.outv, grad_x, grad_v, ctx.h, ctx.ds,
+                                            pos0=ctx.x0, flags=FLAGS)
+        return (drif if need_rif else None, dx0 if need_x else None, dv0 if need_v else None, None, None)
+
+
+class ADSDFTracerC(torch.autograd.Function):
+    """reference core/tracer.py:247-291"""
+
+    @staticmethod
+    def forward(ctx, rif, sdf, x, v, h, ds):
+        ctx.rif = rif.detach()
+        ctx.sdf = sdf.detach()
+        ctx.h, ctx.ds = h, ds
+        ctx.x0 = x.detach()
+        ctx.outx, ctx.outv = ops.trace_sdf(ctx.rif, ctx.sdf, x, v, h, ds, flags=FLAGS)
+        return ctx.outx, ctx.outv
+
+    @staticmethod
+    def backward(ctx, grad_x, grad_v):
+        need_rif, _, need_x, need_v = ctx.needs_input_grad[:4]
+        if not (need_x or need_v):
+            drif = ops.backtrace_sdf(ctx.rif, ctx.sdf, ctx.outx, ctx.outv, grad_x, grad_v, ctx.h, ctx.ds,
+                                     flags=FLAGS)
+            return drif, None, None, None, None, None
+        drif, dx0, dv0 = ops.backtrace_rays(ctx.rif, ctx.outx, ctx.outv, grad_x, grad_v, ctx.h, ctx.ds,
+                                            pos0=ctx.x0, sdf=ctx.sdf, flags=FLAGS)
+        return (drif if need_rif else None, None, dx0 if need_x else None, dv0 if need_v else None,
+                None, None)
+
+
+# Remaining tape-autodiff names of the reference (core/tracer.py:71-244): same signatures,
+# served by the adjoint (rif gradient only).
 ADPlaneTracerC = BackPlaneTracerC
 ADTargetTracerC = BackTargetTracerC
-ADSDFTracerC = BackSDFTracerC
 ADCableTracerC = BackCableTracerC

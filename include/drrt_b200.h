@@ -151,6 +151,20 @@ int drrt_backtrace_cable(const float *rif, int res, float radius, float length, 
                          float ds, float *grad, void *scratch, int64_t *stats, unsigned flags,
                          drrt_stream_t stream);
 
+/* drrt_backtrace_rays <- the ray-state half of ADTracerC.backward / ADSDFTracerC.backward
+ * (reference core/tracer.py:53-60, :247-291: enoki.gradient(ctx.x), enoki.gradient(ctx.v)):
+ * the same adjoint pass as drrt_backtrace (sdf == NULL) / drrt_backtrace_sdf, which in
+ * addition writes dL/dpos and dL/dvel of the LAUNCH state (N x 3 each, `layout`) from the
+ * final co-state: dpos = lambda, dvel = mu + (k - 1) ds lambda, k = number of straight
+ * steps the forward ray took outside the volume before its first in-bounds sample
+ * (recovered from `pos0`, the launch positions; pos0 == NULL means k = 0, i.e. rays
+ * launched on their first in-bounds sample).  Exact for rays launched outside or on the
+ * boundary of the volume -- the only kind the reference's sources produce. */
+int drrt_backtrace_rays(const float *rif, const float *sdf, int W, int H, int D, const float *xt,
+                        const float *vt, const float *dx, const float *dv, const float *pos0, int64_t N,
+                        int layout, float h, float ds, float *grad, float *dpos, float *dvel,
+                        void *scratch, int64_t *stats, unsigned flags, drrt_stream_t stream);
+
 /* ---- volume primitives (parity probes; reference src/test.cpp:61-101) -------
  * drrt_volume_eval   <- volume::eval_grad + eval_hess (src/volume.cpp:101-181, :40-99)
  *                       hess = (N,3): d2/dxdy, d2/dxdz, d2/dydz

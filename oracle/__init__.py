@@ -164,6 +164,23 @@ class _Lib:
         self._check(rc)
         return g.reshape(rif.shape)
 
+    def backtrace_rays(self, rif, xt, vt, dx, dv, h, ds, pos0=None, sdf=None, res=None):
+        """port / port64 only: (grad, dL/dpos, dL/dvel), see eikonal_oracle.c backtrace_rays."""
+        rif = self._a(rif); W, H, D = self._res(rif, res)
+        xt = self._a(xt); vt = self._a(vt); dx = self._a(dx); dv = self._a(dv); N = xt.shape[0]
+        g = np.empty(rif.size, dtype=self.real)
+        dpos = np.empty((N, 3), dtype=self.real); dvel = np.empty((N, 3), dtype=self.real)
+        null = POINTER(self.creal)()
+        p0 = self._a(pos0) if pos0 is not None else None
+        sd = self._a(sdf) if sdf is not None else None
+        rc = self._fn("backtrace_rays")(self._p(rif), self._p(sd) if sd is not None else null, W, H, D,
+                                        self._p(xt), self._p(vt), self._p(dx), self._p(dv),
+                                        self._p(p0) if p0 is not None else null, _i64(N),
+                                        self.creal(h), self.creal(ds), self._p(g), self._p(dpos),
+                                        self._p(dvel))
+        self._check(rc)
+        return g.reshape(rif.shape), dpos, dvel
+
     def backtrace_cable(self, rif, radius, length, xt, vt, dx, dv, ds):
         rif = self._a(rif).ravel()
         xt = self._a(xt); vt = self._a(vt); dx = self._a(dx); dv = self._a(dv); N = xt.shape[0]

@@ -575,7 +575,8 @@ static inline void adj_update(real *la, real *mu, real ds, real dn, real n, cons
  * (ext/enoki/include/enoki/dynamic.h:518-535). */
 static int64_t backtrace_grid(const real *rif, const real *sdf, int W, int H, int D,
                               const real *xt, const real *vt, const real *dx, const real *dv,
-                              int64_t N, real h, real ds, real *grad) {
+                              int64_t N, real h, real ds, real *grad, const real *pos0, real *dpos,
+                              real *dvel) {
   int64_t G = (int64_t) W * H * D;
   vol_t grid = vol_make((real *) rif, W, H, D, h);
   vol_t gradv = vol_make(grad, W, H, D, h);
@@ -584,6 +585,15 @@ static int64_t backtrace_grid(const real *rif, const real *sdf, int W, int H, in
   adj_state_t s = adj_alloc(N, xt, vt, dx, dv, ds);
   int *sidx = (int *) malloc(sizeof(int) * 8 * (size_t) (N ? N : 1));
   real *sterm = (real *) malloc(sizeof(real) * 16 * (size_t) (N ? N : 1));
+  /* ray gradients (not in the reference's backtrace; see backtrace_rays below):
+   * (x_k, v_k) of the last sample that updated lambda / mu */
+  real *xl = 0, *vl = 0;
+  if (dpos) {
+    xl = (real *) malloc(sizeof(real) * 3 * (size_t) (N ? N : 1));
+    vl = (real *) malloc(sizeof(real) * 3 * (size_t) (N ? N : 1));
+    memcpy(xl, xt, sizeof(real) * 3 * (size_t) N);
+    memcpy(vl, vt, sizeof(real) * 3 * (size_t) N);
+  }
   int64_t live_steps = 0;
   for (int64_t r = 0; r < N; ++r) {
     real nv[3] = {-s.v[3 * r], -s.v[3 * r + 1], -s.v[3 * r + 2]};
@@ -631,25 +641,56 @@ static int64_t backtrace_grid(const real *rif, const real *sdf, int W, int H, in
       vol_splat_terms(&gradv, x, dn * ds, dnx, sidx + 8 * r, sterm + 16 * r);
       real Hm[9] = {0, hx[0], hx[1], hx[0], 0, hx[2], hx[1], hx[2], 0};
       adj_update(la, mu, ds, dn, n, nx, Hm);                              /* :434-435 */
+      if (dpos) for (int k = 0; k < 3; ++k) { xl[3 * r + k] = x[k]; vl[3 * r + k] = s.v[3 * r + k]; }
     }
     for (int t = 0; t < 16; ++t)                                          /* src/volume.cpp:217-243 */
       for (int64_t r = 0; r < N; ++r)
         if (s.active[r]) grad[sidx[8 * r + (t & 7)]] += sterm[16 * r + t];
+  }
+  if (dpos) {
+    for (int64_t r = 0; r < N; ++r) {
+      real k = 0;
+      const real *a = xl + 3 * r, *b = vl + 3 * r;
+      if (pos0) {
+        real num = (a[0] - pos0[3 * r]) * b[0] + (a[1] - pos0[3 * r + 1]) * b[1] + (a[2] - pos0[3 * r + 2]) * b[2];
+        real den = ds * (b[0] * b[0] + b[1] * b[1] + b[2] * b[2]);
+        k = den > 0 ? (real) rint((double) (num / den)) : 0;
+      }
+      real t = (k - 1) * ds;
+      for (int c = 0; c < 3; ++c) {
+        dpos[3 * r + c] = s.la[3 * r + c];
+        dvel[3 * r + c] = s.mu[3 * r + c] + t * s.la[3 * r + c];
+      }
+    }
+    free(xl); free(vl);
   }
   free(sidx); free(sterm);
   adj_free(&s);
   return live_steps;
 }
 
+/* NOT a reference function: the adjoint's final co-state mapped to dL/dpos, dL/dvel of
+ * the launch state -- what ADTracerC.backward returns through enoki's tape (reference
+ * core/tracer.py:53-60).  After sample x_k has been processed la = dL/dx_k and
+ * mu = dL/dv_{k-1}; before x_k the forward ray flew straight (masked gathers,
+ * src/tracer.cpp:66-71), so dL/dpos = la and dL/dvel = mu + (k-1) ds la with k the
+ * number of straight steps from pos0 to x_k (k = 0 without pos0).  Pinned against a
+ * float64 tape differentiation of the forward loop in tests (oracle/ad_oracle.py). */
+int64_t SYM(backtrace_rays)(const real *rif, const real *sdf, int W, int H, int D, const real *xt,
+                            const real *vt, const real *dx, const real *dv, const real *pos0,
+                            int64_t N, real h, real ds, real *grad, real *dpos, real *dvel) {
+  return backtrace_grid(rif, sdf, W, H, D, xt, vt, dx, dv, N, h, ds, grad, pos0, dpos, dvel);
+}
+
 int64_t SYM(backtrace)(const real *rif, int W, int H, int D, const real *xt, const real *vt,
                        const real *dx, const real *dv, int64_t N, real h, real ds, real *grad) {
-  return backtrace_grid(rif, 0, W, H, D, xt, vt, dx, dv, N, h, ds, grad);
+  return backtrace_grid(rif, 0, W, H, D, xt, vt, dx, dv, N, h, ds, grad, 0, 0, 0);
 }
 
 int64_t SYM(backtrace_sdf)(const real *rif, const real *sdf, int W, int H, int D, const real *xt,
                            const real *vt, const real *dx, const real *dv, int64_t N, real h,
                            real ds, real *grad) {
-  return backtrace_grid(rif, sdf, W, H, D, xt, vt, dx, dv, N, h, ds, grad);
+  return backtrace_grid(rif, sdf, W, H, D, xt, vt, dx, dv, N, h, ds, grad, 0, 0, 0);
 }
 
 /* Tracer::backtrace_cable, src/tracer.cpp:511-567 */
