@@ -20,6 +20,7 @@ DRRT_ACCUMULATE = 1 << 2
 DRRT_FAST_ARITH = 1 << 3
 DRRT_WARP_AGGREGATION = 1 << 4
 DRRT_NO_INTERLEAVE = 1 << 5
+DRRT_SENSOR_FAR = 1 << 6
 
 
 def DRRT_AGG_RUN(n: int) -> int:
@@ -53,6 +54,8 @@ PROTOTYPES = {
     "drrt_cylinder_splat": (c_int, [_P, _I, _F, _F, _P, _P, _P, _L, _I, _P]),
     "drrt_adam_step": (c_int, [_P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _F, _F, _F, _U, _P]),
     "drrt_upres_volume": (c_int, [_P, _I, _I, _I, _P, _I, _I, _I, _P]),
+    "drrt_sensor_splat": (c_int, [_P, _P, _P, _F, _L, _I, _P, _P, _P, _P, _I, _F, _P, _U, _P]),
+    "drrt_sensor_splat_backward": (c_int, [_P, _P, _P, _F, _L, _I, _P, _P, _P, _P, _I, _F, _P, _P, _P, _P, _U, _P]),
     "drrt_trace_host": (c_int, [_P, _I, _I, _I, _P, _P, _L, _I, _F, _F, _P, _P, _P, _U]),
     "drrt_backtrace_host": (c_int, [_P, _I, _I, _I, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, _U]),
     "drrt_host_cache_grid": (None, [_I]),

@@ -305,6 +305,58 @@ int drrt_backtrace_cable(const float *rif, int res, float radius, float length, 
   return check_launch("backtrace_cable");
 }
 
+namespace {
+int sensor_common(bool backward, const float *x, const float *v, const float *e, float e0, int64_t N, int layout,
+                  const float *plane_p, const float *plane_n, const float *t1, const float *t2, int res,
+                  float span, unsigned flags, float *image, const float *dimage, float *dx, float *dv,
+                  float *de, cudaStream_t s) {
+  const bool far = (flags & DRRT_SENSOR_FAR) != 0;
+  if (N < 0) return fail(DRRT_ERR_INVALID_ARGUMENT, "negative ray count");
+  if (layout != DRRT_SOA && layout != DRRT_AOS) return fail(DRRT_ERR_INVALID_ARGUMENT, "layout must be DRRT_SOA or DRRT_AOS");
+  if (res <= 0 || !(span > 0.f)) return fail(DRRT_ERR_INVALID_ARGUMENT, "sensor: res and span must be positive");
+  if (!plane_n || !t1 || !t2 || (!far && !plane_p)) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL plane vector");
+  SensorArgs a;
+  memset(&a, 0, sizeof a);
+  for (int k = 0; k < 3; ++k) {
+    a.p[k] = plane_p ? plane_p[k] : 0.f; a.n[k] = plane_n[k]; a.t1[k] = t1[k]; a.t2[k] = t2[k];
+  }
+  a.x = x; a.v = v; a.e = e; a.e0 = e0; a.N = N; a.layout = layout; a.res = res;
+  a.offset = 0.5f * span;
+  a.rcp_h = (float) res / span;
+  if (!backward) {
+    if (!image) return fail(DRRT_ERR_INVALID_ARGUMENT, "image is NULL");
+    if (!(flags & DRRT_ACCUMULATE)) CU_TRY(cudaMemsetAsync(image, 0, sizeof(float) * (size_t) res * res, s));
+  } else if (!dimage) {
+    return fail(DRRT_ERR_INVALID_ARGUMENT, "dimage is NULL");
+  }
+  if (N == 0) return DRRT_OK;
+  if (!v || (!far && !x)) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL ray buffer");
+  a.image = image; a.dimage = dimage; a.dx = far ? nullptr : dx; a.dv = dv; a.de = de;
+  if (backward) {
+    if (far && dx) CU_TRY(cudaMemsetAsync(dx, 0, sizeof(float) * 3 * (size_t) N, s));  // far field ignores x
+    g_launches += launch_sensor_splat_bwd(far, a, s);
+  } else {
+    g_launches += launch_sensor_splat(far, a, s);
+  }
+  return check_launch("sensor_splat");
+}
+}  // namespace
+
+int drrt_sensor_splat(const float *x, const float *v, const float *e, float e0, int64_t N, int layout,
+                      const float *plane_p, const float *plane_n, const float *t1, const float *t2, int res,
+                      float span, float *image, unsigned flags, drrt_stream_t stream) {
+  return sensor_common(false, x, v, e, e0, N, layout, plane_p, plane_n, t1, t2, res, span, flags, image, nullptr,
+                       nullptr, nullptr, nullptr, (cudaStream_t) stream);
+}
+
+int drrt_sensor_splat_backward(const float *x, const float *v, const float *e, float e0, int64_t N, int layout,
+                               const float *plane_p, const float *plane_n, const float *t1, const float *t2,
+                               int res, float span, const float *dimage, float *dx, float *dv, float *de,
+                               unsigned flags, drrt_stream_t stream) {
+  return sensor_common(true, x, v, e, e0, N, layout, plane_p, plane_n, t1, t2, res, span, flags, nullptr, dimage,
+                       dx, dv, de, (cudaStream_t) stream);
+}
+
 int drrt_adam_step(float *n, const float *grad, float *exp_avg, float *exp_avg_sq, int S0, int S1, int S2,
                    int step, float lr, float beta1, float beta2, float eps, float clamp_min,
                    unsigned flags, drrt_stream_t stream) {

@@ -69,6 +69,24 @@ struct CableArgs {
   int64_t *stats;
 };
 
+// sensor epilogue, drrt_sensor_kernels.cu
+struct SensorArgs {
+  const float *x, *v;   // ray state at the volume exit (x unused in far-field mode)
+  const float *e;       // per-ray radiance, or NULL -> e0
+  float e0;
+  int64_t N;
+  int layout;
+  float p[3], n[3], t1[3], t2[3];  // plane origin, normal, tangents (t1 = n x t2)
+  int res;
+  float offset;         // span / 2 (near) or sin(angle_span / 2) (far)
+  float rcp_h;          // res / span resp. res / (2 offset)
+  float *image;         // forward: res x res, accumulated into
+  const float *dimage;  // backward: dL/dimage
+  float *dx, *dv, *de;  // backward outputs (each nullable)
+};
+int launch_sensor_splat(bool far, const SensorArgs &a, cudaStream_t s);
+int launch_sensor_splat_bwd(bool far, const SensorArgs &a, cudaStream_t s);
+
 // kind: 0 plain, 1 plane, 2 target, 3 sdf.  Returns the number of kernels launched.
 // arith: 0 fast polynomial, 1 reference-literal, 2 exact-trajectory (default)
 int launch_trace(int kind, int arith, const TraceArgs &a, cudaStream_t s);

@@ -1,0 +1,124 @@
+"""Sensor epilogue with the names and call signatures of the reference's
+``core/sensor.py``.
+
+``generate_sensor`` / ``generate_inf_sensor`` run as ONE fused CUDA kernel each way
+(``drrt_sensor_splat`` / ``drrt_sensor_splat_backward``, ``csrc/drrt_sensor_kernels.cu``)
+instead of the reference's chain of torch ops over ``(N, 16)`` temporaries
+differentiated by autograd (reference core/sensor.py:5-54 over core/grid.py:38-151).
+There is no CPU path: tensors must be CUDA float32.
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+from ctypes import c_void_p
+
+import torch
+
+from . import _capi
+from ._capi import DRRT_AOS, DRRT_SENSOR_FAR
+
+__all__ = ["trace_rays_to_plane", "get_tan_vecs", "generate_sensor", "generate_inf_sensor"]
+
+
+def trace_rays_to_plane(rays, plane):
+    """reference core/sensor.py:195-202 (elementwise torch; differentiable)."""
+    x, v = rays
+    p, n = plane
+    t = ((p - x) * n).sum(-1, keepdim=True) / (v * n).sum(-1, keepdim=True)
+    return (x + t * v), v
+
+
+def get_tan_vecs(n, t=None):
+    """reference core/sensor.py:218-229."""
+    if t is None:
+        t2 = torch.zeros_like(n)
+        if torch.abs(n)[0, -1] > 0.001:
+            t2[0, 0] = 1
+        else:
+            t2[0, -1] = 1
+    else:
+        t2 = t
+    t1 = torch.cross(n, t2, dim=1)
+    return t1, t2
+
+
+def _host3(t):
+    a = (ctypes.c_float * 3)()
+    vals = t.detach().reshape(-1)[:3].to("cpu", torch.float32).tolist()
+    a[0], a[1], a[2] = vals
+    return a
+
+
+def _rayten(t, name):
+    if not t.is_cuda or t.dtype != torch.float32:
+        raise RuntimeError(f"{name}: expected a CUDA float32 tensor (there is no CPU path)")
+    if t.dim() != 2 or t.shape[1] != 3:
+        raise RuntimeError(f"{name}: expected shape (N, 3), got {tuple(t.shape)}")
+    return t.detach().contiguous()
+
+
+class _SensorSplat(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, v, e, plane, res, span, far):
+        xd, vd = _rayten(x, "x"), _rayten(v, "v")
+        N = xd.shape[0]
+        if vd.shape[0] != N:
+            raise RuntimeError("x and v: ray counts differ")
+        if isinstance(e, torch.Tensor) and e.numel() > 1:
+            ed = e.detach().to(torch.float32).contiguous().reshape(-1)
+            if ed.numel() != N or not ed.is_cuda:
+                raise RuntimeError("e: expected a scalar or a CUDA tensor with one value per ray")
+            e0 = 0.0
+        else:
+            ed, e0 = None, float(e)
+        ctx.args = (xd, vd, ed, e0, plane, int(res), float(span), DRRT_SENSOR_FAR if far else 0)
+        image = torch.empty((int(res), int(res)), dtype=torch.float32, device=xd.device)
+        p, n, t1, t2 = plane
+        with torch.cuda.device(xd.device):
+            s = c_void_p(torch.cuda.current_stream(xd.device).cuda_stream)
+            _capi.check(_capi.load().drrt_sensor_splat(
+                c_void_p(xd.data_ptr()), c_void_p(vd.data_ptr()), c_void_p(ed.data_ptr() if ed is not None else 0),
+                e0, N, DRRT_AOS, p, n, t1, t2, int(res), float(span), c_void_p(image.data_ptr()),
+                ctx.args[7], s))
+        return image
+
+    @staticmethod
+    def backward(ctx, dimage):
+        xd, vd, ed, e0, plane, res, span, flags = ctx.args
+        p, n, t1, t2 = plane
+        N = xd.shape[0]
+        dimage = dimage.detach().to(torch.float32).contiguous()
+        need_x, need_v, need_e = ctx.needs_input_grad[:3]
+        dx = torch.empty_like(xd) if need_x else None
+        dv = torch.empty_like(vd) if need_v else None
+        de = torch.empty(N, dtype=torch.float32, device=xd.device) if (need_e and ed is not None) else None
+        with torch.cuda.device(xd.device):
+            s = c_void_p(torch.cuda.current_stream(xd.device).cuda_stream)
+            _capi.check(_capi.load().drrt_sensor_splat_backward(
+                c_void_p(xd.data_ptr()), c_void_p(vd.data_ptr()), c_void_p(ed.data_ptr() if ed is not None else 0),
+                e0, N, DRRT_AOS, p, n, t1, t2, res, span, c_void_p(dimage.data_ptr()),
+                c_void_p(dx.data_ptr() if dx is not None else 0), c_void_p(dv.data_ptr() if dv is not None else 0),
+                c_void_p(de.data_ptr() if de is not None else 0), flags, s))
+        return dx, dv, de, None, None, None, None
+
+
+def _plane(plane, tangent):
+    p, n = plane
+    if n.dim() != 2 or n.shape[0] != 1:
+        raise RuntimeError("generate_sensor: one plane per call, p and n shaped (1, 3) as in the reference")
+    t1, t2 = get_tan_vecs(n, tangent)
+    return _host3(p), _host3(n), _host3(t1), _host3(t2)
+
+
+def generate_sensor(rays, e, plane, res, span, tangent=None):
+    """reference core/sensor.py:5-28 -> (res, res) image; differentiable w.r.t. the rays (and e)."""
+    x, v = rays
+    return _SensorSplat.apply(x, v, e, _plane(plane, tangent), res, span, False)
+
+
+def generate_inf_sensor(rays, e, plane, res, angle_span=120, tangent=None):
+    """reference core/sensor.py:31-54 -> (res, res) far-field image over sin(angle) coordinates."""
+    x, v = rays
+    ang_cut = math.sin(0.5 * math.radians(angle_span))
+    return _SensorSplat.apply(x, v, e, _plane(plane, tangent), res, 2.0 * ang_cut, True)

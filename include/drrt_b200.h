@@ -201,6 +201,29 @@ int drrt_adam_step(float *n, const float *grad, float *exp_avg, float *exp_avg_s
 int drrt_upres_volume(const float *src, int s0, int s1, int s2, float *dst, int d0, int d1, int d2,
                       drrt_stream_t stream);
 
+/* ---- sensor epilogue (the step after every trace in the reference's drivers) -------
+ * drrt_sensor_splat <- sensor.generate_sensor (reference core/sensor.py:5-28: rays to the
+ *                      sensor plane :195-202, |v.n| foreshortening, projection on the
+ *                      tangents, Grid.Splat(average=False) core/grid.py:133-151 with the 4x4
+ *                      radial-tent stencil core/grid.py:38-66, :80-85), and with
+ *                      DRRT_SENSOR_FAR <- sensor.generate_inf_sensor (core/sensor.py:31-54;
+ *                      `span` is then 2 sin(angle_span / 2), x and plane_p are ignored).
+ *                      `image` is res x res, row index along t1 (= n x t2), column along t2;
+ *                      zero-filled first unless DRRT_ACCUMULATE.  `e` = per-ray radiance
+ *                      (device, N floats) or NULL for the constant e0.  The four plane
+ *                      vectors are HOST pointers to 3 floats.
+ * drrt_sensor_splat_backward <- what torch autograd derives for the same call: given
+ *                      dL/dimage writes dL/dx, dL/dv (N x 3, `layout`) and dL/de (N); each
+ *                      output is nullable. */
+enum { DRRT_SENSOR_FAR = 1u << 6 };
+int drrt_sensor_splat(const float *x, const float *v, const float *e, float e0, int64_t N, int layout,
+                      const float *plane_p, const float *plane_n, const float *t1, const float *t2, int res,
+                      float span, float *image, unsigned flags, drrt_stream_t stream);
+int drrt_sensor_splat_backward(const float *x, const float *v, const float *e, float e0, int64_t N, int layout,
+                               const float *plane_p, const float *plane_n, const float *t1, const float *t2,
+                               int res, float span, const float *dimage, float *dx, float *dv, float *de,
+                               unsigned flags, drrt_stream_t stream);
+
 /* ---- host-buffer entry points (what a non-torch binding of the reference API
  * calls; device memory is managed inside the library and cached per thread) --- */
 int drrt_trace_host(const float *rif, int W, int H, int D, const float *pos, const float *vel,
