@@ -357,6 +357,34 @@ int drrt_sensor_splat_backward(const float *x, const float *v, const float *e, f
                        dx, dv, de, (cudaStream_t) stream);
 }
 
+int drrt_plane_source_rand(const float *offset, uint64_t seed, const float *view_rot, int nviews, int P0, int P1,
+                           int spp, float width, float sensor_dist, int independent, const float *post_rot,
+                           float post_span, float *x, float *v, float *planes, uint8_t *keep,
+                           drrt_stream_t stream) {
+  if (nviews < 0 || P0 <= 0 || P1 <= 0 || spp <= 0) return fail(DRRT_ERR_INVALID_ARGUMENT, "plane source: bad view / pixel / sample count");
+  if (nviews == 0) return DRRT_OK;
+  if (!view_rot || !x || !v || !planes) return fail(DRRT_ERR_INVALID_ARGUMENT, "plane source: NULL buffer");
+  SourceArgs a;
+  memset(&a, 0, sizeof a);
+  a.offset = offset; a.seed = seed; a.P0 = P0; a.P1 = P1; a.spp = spp;
+  a.rays_per_view = (int64_t) spp * P0 * P1;
+  a.width = width; a.sensor_dist = sensor_dist; a.independent = independent;
+  if (post_rot) {
+    a.has_post = 1; a.post_span = post_span;
+    memcpy(a.post_rot, post_rot, sizeof(float) * 9);
+  }
+  for (int first = 0; first < nviews; first += kSourceMaxViews) {
+    const int nv = nviews - first < kSourceMaxViews ? nviews - first : kSourceMaxViews;
+    a.first_view = first; a.nviews = nv;
+    memcpy(a.view_rot, view_rot + 9 * (size_t) first, sizeof(float) * 9 * (size_t) nv);
+    const size_t r0 = (size_t) first * (size_t) a.rays_per_view;
+    a.x = x + 3 * r0; a.v = v + 3 * r0; a.planes = planes + 9 * r0;
+    a.keep = keep ? keep + r0 : nullptr;
+    g_launches += launch_plane_source(a, (cudaStream_t) stream);
+  }
+  return check_launch("plane_source");
+}
+
 int drrt_adam_step(float *n, const float *grad, float *exp_avg, float *exp_avg_sq, int S0, int S1, int S2,
                    int step, float lr, float beta1, float beta2, float eps, float clamp_min,
                    unsigned flags, drrt_stream_t stream) {

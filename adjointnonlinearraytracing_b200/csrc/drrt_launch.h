@@ -87,6 +87,24 @@ struct SensorArgs {
 int launch_sensor_splat(bool far, const SensorArgs &a, cudaStream_t s);
 int launch_sensor_splat_bwd(bool far, const SensorArgs &a, cudaStream_t s);
 
+// on-device ray generation, drrt_source_kernels.cu
+constexpr int kSourceMaxViews = 32;  // views per launch (their rotations travel as kernel parameters)
+struct SourceArgs {
+  const float *offset;   // device uniforms [total views][2*spp][P0][P1], or NULL -> Philox(seed)
+  uint64_t seed;
+  int first_view, nviews;  // this launch covers views [first_view, first_view + nviews)
+  int P0, P1, spp;
+  int64_t rays_per_view;   // spp * P0 * P1
+  float width, sensor_dist;
+  int independent;
+  int has_post;
+  float post_rot[9], post_span;
+  float view_rot[9 * kSourceMaxViews];
+  float *x, *v, *planes;   // outputs of this launch: (n,3), (n,3), (n,3,3)
+  uint8_t *keep;           // circle mask of this launch, or NULL
+};
+int launch_plane_source(const SourceArgs &a, cudaStream_t s);
+
 // kind: 0 plain, 1 plane, 2 target, 3 sdf.  Returns the number of kernels launched.
 // arith: 0 fast polynomial, 1 reference-literal, 2 exact-trajectory (default)
 int launch_trace(int kind, int arith, const TraceArgs &a, cudaStream_t s);

@@ -1,0 +1,112 @@
+// on-device ray generation -- the step before every trace in the
+// reference's drivers, which build the batch with CPU torch ops and copy it to the GPU each
+// iteration (reference core/luneburg_opt.py:53-59, core/image_opt.py:44-52).
+//
+//   plane_source3_rand     reference core/source.py:54-69  (jittered pixel grid on a plane)
+//   rotate_pts_to_source   reference core/source.py:275-293 (view rotation, launch plane,
+//                                                          sensor plane triple)
+//   rand_rays_in_sphere    reference core/source.py:352-357 (one plane source per view)
+//   rand_rays_cube         reference core/source.py:398-412 (4 + 2 axis views)
+//   random_rotate_ic       reference core/source.py:555-563 (one rigid rotation of the batch)
+//
+// One thread per ray writes x, v and the (3,3) plane triple: 60 B per ray, HBM-write bound.
+// The jitter is either read from a caller-supplied uniform array (the layout of the
+// reference's torch.rand(2*spp, P0, P1) per view -- used by the parity tests) or drawn
+// in-kernel from Philox4x32-10 keyed by (seed, view, sample index).
+#include "drrt_device.cuh"
+#include "drrt_launch.h"
+
+namespace drrt {
+
+namespace {
+
+__device__ __forceinline__ void philox_round(uint32_t &c0, uint32_t &c1, uint32_t &c2, uint32_t &c3, uint32_t k0,
+                                             uint32_t k1) {
+  const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+  const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+  const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+  c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+}
+
+// Philox4x32-10 (Salmon et al., SC'11): 4 x 32 random bits for one 128-bit counter.
+__device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                               uint32_t k1) {
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    philox_round(c0, c1, c2, c3, k0, k1);
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  return make_uint4(c0, c1, c2, c3);
+}
+
+// uniform in [0, 1) with 24 random bits, like torch.rand for float32
+__device__ __forceinline__ float u01(uint32_t bits) { return (float) (bits >> 8) * (1.0f / 16777216.0f); }
+
+__device__ __forceinline__ f3 rot(const float *R, f3 a) {  // a @ R^T = R a, R row-major
+  return f3{R[0] * a.x + R[1] * a.y + R[2] * a.z, R[3] * a.x + R[4] * a.y + R[5] * a.z,
+            R[6] * a.x + R[7] * a.y + R[8] * a.z};
+}
+
+__global__ void __launch_bounds__(256) plane_source_kernel(SourceArgs a) {
+  const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= a.rays_per_view * a.nviews) return;
+  const int view = (int) (r / a.rays_per_view);
+  const int64_t q = r - (int64_t) view * a.rays_per_view;  // (s * P0 + i) * P1 + j
+  const int j = (int) (q % a.P1);
+  const int i = (int) ((q / a.P1) % a.P0);
+  float ua, ub;
+  if (a.offset) {  // torch.rand(2*spp, P0, P1) of this view: [:spp] jitters axis 0, [spp:] axis 1
+    const float *o = a.offset + (int64_t) (a.first_view + view) * 2 * a.rays_per_view;
+    ua = o[q]; ub = o[a.rays_per_view + q];
+  } else {
+    const uint4 b = philox4x32_10((uint32_t) q, (uint32_t) (q >> 32), (uint32_t) (a.first_view + view), 0u,
+                                  (uint32_t) a.seed, (uint32_t) (a.seed >> 32));
+    ua = u01(b.x); ub = u01(b.y);
+  }
+  const float w = a.width;
+  f3 p;
+  p.y = 0.f;
+  if (a.independent) {  // core/source.py:60-63
+    p.x = ua * w - 0.5f * w;
+    p.z = ub * w - 0.5f * w;
+  } else {              // core/source.py:56-57, :65-68
+    p.x = w * ((float) i / (float) a.P0 - 0.5f) + (ua * w) / (float) a.P0;
+    p.z = w * ((float) j / (float) a.P1 - 0.5f) + (ub * w) / (float) a.P1;
+  }
+  if (a.keep) a.keep[r] = sqrtf(p.x * p.x + p.z * p.z) < 0.5f * w ? 1 : 0;  // circle: core/source.py:277-280
+  const float *R = a.view_rot + 9 * view;
+  const float hw = 0.5f * w;
+  f3 x = rot(R, p);                       // :284
+  f3 v = rot(R, f3{0.f, 1.f, 0.f});       // :285
+  f3 t = rot(R, f3{0.f, 0.f, 1.f});       // :286
+  x.x += hw; x.y += hw; x.z += hw;
+  x.x -= w * v.x * 0.5f; x.y -= w * v.y * 0.5f; x.z -= w * v.z * 0.5f;   // :287
+  const float pd = a.sensor_dist + hw;
+  f3 px = {pd * v.x + hw, pd * v.y + hw, pd * v.z + hw};                 // :290
+  if (a.has_post) {  // random_rotate_ic, core/source.py:555-563: rotate about the volume centre span / 2
+    const float c = 0.5f * a.post_span;
+    f3 d = {x.x - c, x.y - c, x.z - c};
+    x = rot(a.post_rot, d); x.x += c; x.y += c; x.z += c;
+    d = f3{px.x - c, px.y - c, px.z - c};
+    px = rot(a.post_rot, d); px.x += c; px.y += c; px.z += c;
+    v = rot(a.post_rot, v);
+    t = rot(a.post_rot, t);
+  }
+  float *ox = a.x + 3 * r, *ov = a.v + 3 * r, *op = a.planes + 9 * r;
+  ox[0] = x.x; ox[1] = x.y; ox[2] = x.z;
+  ov[0] = v.x; ov[1] = v.y; ov[2] = v.z;
+  op[0] = px.x; op[1] = px.y; op[2] = px.z;   // planes[:, 0] sensor origin
+  op[3] = v.x; op[4] = v.y; op[5] = v.z;      // planes[:, 1] sensor normal
+  op[6] = t.x; op[7] = t.y; op[8] = t.z;      // planes[:, 2] sensor tangent
+}
+
+}  // namespace
+
+int launch_plane_source(const SourceArgs &a, cudaStream_t s) {
+  const int64_t n = a.rays_per_view * a.nviews;
+  if (n <= 0) return 0;
+  plane_source_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(a);
+  return 1;
+}
+
+}  // namespace drrt

@@ -224,6 +224,25 @@ int drrt_sensor_splat_backward(const float *x, const float *v, const float *e, f
                                int res, float span, const float *dimage, float *dx, float *dv, float *de,
                                unsigned flags, drrt_stream_t stream);
 
+/* ---- on-device ray generation (the step before every trace in the reference's drivers) ----
+ * drrt_plane_source_rand <- source.plane_source3_rand + rotate_pts_to_source (reference
+ *     core/source.py:54-69, :275-293) for `nviews` views in one call, which is what
+ *     rand_rays_in_sphere (:352-357) and rand_rays_cube (:398-412) concatenate, optionally
+ *     followed by random_rotate_ic (:555-563).
+ *     view_rot: HOST, nviews x 9 row-major rotation matrices (rotate_ray3, :303-312).
+ *     offset:   DEVICE uniforms in [0,1) laid out [nviews][2*spp][P0][P1] (the reference's
+ *               torch.rand(2*spp, P0, P1) per view), or NULL to draw them in-kernel from
+ *               Philox4x32-10 keyed by (seed, view, sample).
+ *     post_rot: HOST 3x3 applied about (post_span/2)^3 to rays and planes, or NULL.
+ *     Outputs (device): x, v (n,3); planes (n,3,3) = sensor origin, normal, tangent per ray;
+ *     n = nviews*spp*P0*P1, ray index = ((view*spp + s)*P0 + i)*P1 + j.  keep (nullable, n
+ *     bytes): 1 where the un-rotated launch point lies inside the circle of diameter `width`
+ *     (the reference's circle=True filter, :277-280; the caller compacts). */
+int drrt_plane_source_rand(const float *offset, uint64_t seed, const float *view_rot, int nviews, int P0, int P1,
+                           int spp, float width, float sensor_dist, int independent, const float *post_rot,
+                           float post_span, float *x, float *v, float *planes, uint8_t *keep,
+                           drrt_stream_t stream);
+
 /* ---- host-buffer entry points (what a non-torch binding of the reference API
  * calls; device memory is managed inside the library and cached per thread) --- */
 int drrt_trace_host(const float *rif, int W, int H, int D, const float *pos, const float *vel,
