@@ -21,6 +21,8 @@ DRRT_FAST_ARITH = 1 << 3
 DRRT_WARP_AGGREGATION = 1 << 4
 DRRT_NO_INTERLEAVE = 1 << 5
 DRRT_SENSOR_FAR = 1 << 6
+DRRT_NO_FACE_CARRY = 1 << 7
+DRRT_AUTO_INTERLEAVE = 1 << 18
 
 
 def DRRT_AGG_RUN(n: int) -> int:

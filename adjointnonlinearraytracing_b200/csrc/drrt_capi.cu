@@ -97,11 +97,16 @@ int check_rays(int64_t N, int layout, float ds) {
 
 constexpr size_t kFixedTail = 16;
 
-// 0 = off, -1 = measured on the device (default), 2^k = forced (DRRT_INTERLEAVE(n))
+// 0 = off, -1 = measured on the device, 2^k = forced (DRRT_INTERLEAVE(n)).
+// Default: off with the face-carry flush (measured: profiles/r05_facecarry.log -- once the
+// shared face stays in registers the strided ray assignment no longer pays), measured on
+// the device without it (DRRT_NO_FACE_CARRY = the r03/r04 configuration).
 int interleave_of(unsigned flags) {
   if (flags & DRRT_NO_INTERLEAVE) return 0;
   unsigned n = (flags >> 12) & 0x3fu;
-  return n ? (int) n : -1;
+  if (n) return (int) n;
+  if (flags & DRRT_AUTO_INTERLEAVE) return -1;
+  return (flags & DRRT_NO_FACE_CARRY) ? -1 : 0;
 }
 
 // 0 fast polynomial, 1 reference-literal, 2 exact-trajectory (default)
@@ -167,6 +172,7 @@ int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, i
   a.N = N; a.layout = layout; a.ds = ds; a.stats = stats;
   a.max_steps = cap_grid(2.0f, h, W, H, D, ds);
   a.agg_policy = (int) ((flags >> 8) & 0xfu);  // experimental: DRRT_AGG_RUN(n), 0 = adaptive
+  a.face_carry = (flags & DRRT_NO_FACE_CARRY) ? 0 : 1;
   unsigned long long *fixed = nullptr;
   unsigned *max_bits = nullptr;
   if (det) {

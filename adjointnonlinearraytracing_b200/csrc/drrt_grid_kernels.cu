@@ -281,6 +281,44 @@ __device__ __forceinline__ void flush_direct(const Accum &out, const CellAddr &c
   for (int k = 0; k < 8; ++k) out.add(ca.at(k), acc[k]);
 }
 
+// Face carry.  When a ray steps into a face-adjacent cell, four of the eight corner
+// accumulators belong to the face the two cells share: they stay in registers (moved to
+// the new cell's slots) and only the four corners left behind are flushed -- half the
+// atomics per cell visit along the dominant direction of travel.  Adjacency is read off
+// the addresses themselves (same strides, base shifted by exactly one stride), so clamped
+// cells at and beyond the grid boundary simply take the full flush.
+// Returns true when accumulators were carried (P still holds unflushed data).
+template <class Accum>
+__device__ __forceinline__ bool flush_carry(const Accum &out, const CellAddr &ca, const CellAddr &na, f32x2 P[4]) {
+  const bool same = (na.dx == ca.dx) & (na.dy == ca.dy) & (na.dz == ca.dz);
+  const int d = na.base - ca.base;
+  if (same && ca.dz != 0 && d == -ca.dz) {        // z-: old z0 face becomes the new z1 face
+    out.add(ca.at(4), lo2(P[2])); out.add(ca.at(5), hi2(P[2])); out.add(ca.at(6), lo2(P[3])); out.add(ca.at(7), hi2(P[3]));
+    P[2] = P[0]; P[3] = P[1]; P[0] = P[1] = 0ull;
+  } else if (same && ca.dz != 0 && d == ca.dz) {  // z+
+    out.add(ca.at(0), lo2(P[0])); out.add(ca.at(1), hi2(P[0])); out.add(ca.at(2), lo2(P[1])); out.add(ca.at(3), hi2(P[1]));
+    P[0] = P[2]; P[1] = P[3]; P[2] = P[3] = 0ull;
+  } else if (same && ca.dy != 0 && d == -ca.dy) {  // y-
+    out.add(ca.at(2), lo2(P[1])); out.add(ca.at(3), hi2(P[1])); out.add(ca.at(6), lo2(P[3])); out.add(ca.at(7), hi2(P[3]));
+    P[1] = P[0]; P[3] = P[2]; P[0] = P[2] = 0ull;
+  } else if (same && ca.dy != 0 && d == ca.dy) {   // y+
+    out.add(ca.at(0), lo2(P[0])); out.add(ca.at(1), hi2(P[0])); out.add(ca.at(4), lo2(P[2])); out.add(ca.at(5), hi2(P[2]));
+    P[0] = P[1]; P[2] = P[3]; P[1] = P[3] = 0ull;
+  } else if (same && ca.dx != 0 && d == -ca.dx) {  // x-: x0 corners become x1 corners
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { out.add(ca.at(2 * j + 1), hi2(P[j])); P[j] = pk2(0.f, lo2(P[j])); }
+  } else if (same && ca.dx != 0 && d == ca.dx) {   // x+
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { out.add(ca.at(2 * j), lo2(P[j])); P[j] = pk2(hi2(P[j]), 0.f); }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { out.add(ca.at(2 * j), lo2(P[j])); out.add(ca.at(2 * j + 1), hi2(P[j])); }
+    P[0] = P[1] = P[2] = P[3] = 0ull;
+    return false;
+  }
+  return true;
+}
+
 __device__ __forceinline__ void unpack8(const f32x2 P[4], float acc[8]) {
 #pragma unroll
   for (int j = 0; j < 4; ++j) { acc[2 * j] = lo2(P[j]); acc[2 * j + 1] = hi2(P[j]); }
@@ -467,11 +505,17 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : 
       if (AGG) {
         flush_aggregated(out, ca, P, fl, lane, a.agg_policy, agg);
       } else if (fl) {
-        float acc[8];
-        unpack8(P, acc);
-        flush_direct(out, ca, acc);
+        if (a.face_carry && active) {  // active && fl implies chg: the ray moves on to cell nca
+          have = flush_carry(out, ca, nca, P);
+        } else {
+          float acc[8];
+          unpack8(P, acc);
+          flush_direct(out, ca, acc);
+          P[0] = P[1] = P[2] = P[3] = 0ull;
+          have = false;
+        }
       }
-      if (fl) {
+      if (AGG && fl) {
         P[0] = P[1] = P[2] = P[3] = 0ull;
         have = false;
       }

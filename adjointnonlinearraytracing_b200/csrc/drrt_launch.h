@@ -50,6 +50,7 @@ struct AdjArgs {
   float ds;
   int max_steps;
   int agg_policy;  // warp aggregation: 0 adaptive, 2/4/8 fixed maximum run length
+  int face_carry;  // keep the accumulators of the face shared with the next cell in registers
   const int *interleave_log2;  // device: log2 of the ray interleave, or NULL (identity mapping)
   int64_t *stats;
   // ray gradients: dL/dpos, dL/dvel of the launch state; pos0 nullable

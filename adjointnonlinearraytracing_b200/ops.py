@@ -30,9 +30,10 @@ __all__ = [
 
 def make_flags(reference_arith: bool = False, deterministic: bool = False,
                accumulate: bool = False, fast_arith: bool = False,
-               warp_aggregation: bool = False, interleave=None) -> int:
+               warp_aggregation: bool = False, interleave=None, face_carry: bool = True) -> int:
     """Flag word of the C ABI (include/drrt_b200.h).  Default arithmetic = exact trajectory;
-    `interleave`: None = measured on the device, 0/False = off, 2^k = forced."""
+    `interleave`: None = the library default (off with the face carry), 0/False = off,
+    "auto" = measured on the device, 2^k = forced."""
     if reference_arith and fast_arith:
         raise ValueError("reference_arith and fast_arith are mutually exclusive")
     return ((DRRT_REFERENCE_ARITH if reference_arith else 0)
@@ -40,7 +41,9 @@ def make_flags(reference_arith: bool = False, deterministic: bool = False,
             | (DRRT_ACCUMULATE if accumulate else 0)
             | (DRRT_FAST_ARITH if fast_arith else 0)
             | (DRRT_WARP_AGGREGATION if warp_aggregation else 0)
-            | (0 if interleave is None else DRRT_NO_INTERLEAVE if not interleave else DRRT_INTERLEAVE(interleave)))
+            | (0 if face_carry else _capi.DRRT_NO_FACE_CARRY)
+            | (0 if interleave is None else _capi.DRRT_AUTO_INTERLEAVE if interleave == "auto"
+               else DRRT_NO_INTERLEAVE if not interleave else DRRT_INTERLEAVE(interleave)))
 
 
 def new_stats(device) -> torch.Tensor:

@@ -380,7 +380,7 @@ def run_ours(args):
             "fwd_ms": fwd_ms, "adj_ms": adj_ms,
             "fwd_ray_steps_per_s": s_f / (fwd_ms * 1e-3), "adj_ray_steps_per_s": s_b / (adj_ms * 1e-3),
             "roofline": {
-                "bound": "hbm", "kernel": "backtrace_kernel<sdf=0,A_EXACT,AccumFloat> (ray interleave measured on device)", "achieved": adj_gbs, "peak": peak,
+                "bound": "hbm", "kernel": "backtrace_kernel<sdf=0,A_EXACT,AccumFloat> (face-carry flush, no interleave)", "achieved": adj_gbs, "peak": peak,
                 "unit": "GB/s", "frac": adj_gbs / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_ray_step": BYTES_ADJ,
                 "fwd_kernel": {"achieved": fwd_gbs, "frac": fwd_gbs / peak, "algorithmic_bytes_per_ray_step": BYTES_FWD},

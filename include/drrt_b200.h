@@ -67,8 +67,8 @@ enum {
    * few rays per 10^4 take the other branch at a cell face. */
   DRRT_REFERENCE_ARITH = 1u << 0,
   DRRT_FAST_ARITH = 1u << 3,
-  /* Adjoint only, A/B switches for profiling (defaults: interleave measured on the
-   * device, no warp aggregation).
+  /* Adjoint only, A/B switches for profiling (defaults: face-carry flush, no interleave,
+   * no warp aggregation).
    * DRRT_NO_INTERLEAVE: ray i on thread i instead of the strided assignment that puts
    * the lanes of a warp into different cells.
    * DRRT_WARP_AGGREGATION: pre-sum lanes that flush the same cell with a segmented
@@ -79,6 +79,12 @@ enum {
   DRRT_NO_WARP_AGGREGATION = 0u, /* kept for source compatibility: aggregation is opt-in */
   DRRT_WARP_AGGREGATION = 1u << 4,
   DRRT_NO_INTERLEAVE = 1u << 5,
+  /* DRRT_NO_FACE_CARRY: flush all eight corner accumulators on every cell change instead of
+   * keeping the four of the face shared with the next cell in registers (A/B switch; this
+   * also restores the device-measured interleave as the default, i.e. the r03/r04 kernel).
+   * DRRT_AUTO_INTERLEAVE: measure the interleave on the device even with the face carry. */
+  DRRT_NO_FACE_CARRY = 1u << 7,
+  DRRT_AUTO_INTERLEAVE = 1u << 18,
   /* Adjoint only: accumulate the gradient in 64-bit fixed point so the result is
    * bit-stable from run to run regardless of atomic ordering (and of the ray
    * order / interleave). */

@@ -1,0 +1,43 @@
+"""Dev script (GPU box): one forward + N adjoint launches of a named workload with given flags --
+the thing to put under ncu.
+
+    python tools/gpu_one.py <caustic|cone|fuel|focal|luneburg> <flags> [reps]
+"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+
+import __graft_entry__ as ge
+
+ge.build()
+from adjointnonlinearraytracing_b200 import ops, scenes as sc  # noqa: E402
+from tools.gpu_configs import multiview_rays  # noqa: E402
+
+dev = torch.device("cuda:0")
+T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+CASES = {
+    "caustic": lambda: (256, *sc.rays_collimated(2048)),
+    "cone": lambda: (256, *sc.rays_cone(2048, spread=0.05)),
+    "fuel": lambda: (65, *multiview_rays(32, 64, 16)),
+    "focal": lambda: (512, *sc.rays_collimated(1448)),
+    "luneburg": lambda: (32, *sc.rays_collimated(256)),
+}
+
+if __name__ == "__main__":
+    name = sys.argv[1]
+    flag_list = [int(f, 0) for f in sys.argv[2].split(",")]
+    reps = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+    ng, pos, vel = CASES[name]()
+    rif = T(sc.field_bump(ng)); h = float(sc.grid_spacing(ng)); ds = h / 2
+    pos, vel = T(pos), T(vel)
+    one = torch.ones_like(pos)
+    xt, vt = ops.trace(rif, pos, vel, h, ds)
+    for fl in flag_list:
+        for _ in range(reps):
+            a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+            a.record(); ops.backtrace(rif, xt, vt, one, one, h, ds, flags=fl); b.record()
+            torch.cuda.synchronize()
+            print(f"{name} flags={fl:#x} adj {a.elapsed_time(b):.3f} ms", flush=True)
