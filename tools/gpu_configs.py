@@ -47,9 +47,9 @@ def multiview_rays(n_views, s, spp, seed=0):
     return np.concatenate(P).astype(np.float32), np.concatenate(V).astype(np.float32)
 
 
-def grid_case(name, ng, pos, vel, field=sc.field_bump):
-    rif = T(field(ng)); h = float(sc.grid_spacing(ng)); ds = h / 2
-    pos, vel = T(pos), T(vel)
+def grid_case(name, ng, pos, vel, field=sc.field_bump, step_res=2):
+    rif = T(field(ng)); h = float(sc.grid_spacing(ng)); ds = h / step_res
+    pos, vel = (p if torch.is_tensor(p) else T(p) for p in (pos, vel))
     one = torch.ones_like(pos)
     st = ops.new_stats(dev); xt, vt = ops.trace(rif, pos, vel, h, ds, stats=st); sf, ne = int(st[0]), int(st[1])
     tf = timeit(lambda: ops.trace(rif, pos, vel, h, ds))
@@ -74,13 +74,29 @@ def cable_case(name, res, s, length=5.0):
           f"{sb/tb/1e6:6.1f} G/s | fwd+adj {(sf+sb)/(tf+tb)/1e6:6.1f} G ray-steps/s", flush=True)
 
 
+def luneburg_yaml_rays():
+    """data/params-luneburg.yaml: nbins 128, spp 10, six cube faces, circle filter, random rotation --
+    generated on the device (source.rand_rays_cube)."""
+    from adjointnonlinearraytracing_b200 import source
+    import time
+    torch.manual_seed(0); np.random.seed(0)
+    rot = source.random_rotmat().numpy()
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    (x, v, planes), nr = source.rand_rays_cube((128, 128), 10, 1.0, circle=True, rotmat=rot)
+    torch.cuda.synchronize(); t1 = time.perf_counter()
+    print(f"   (device ray generation: {x.shape[0]} rays in {(t1 - t0) * 1e3:.2f} ms incl. circle compaction)")
+    return x, v
+
+
 def main():
     grid_case("1 Luneburg 32^3, 256^2 rays", 32, *sc.rays_collimated(256), field=sc.field_luneburg)
+    grid_case("1' Luneburg yaml 129^3 ds=h/32", 129, *luneburg_yaml_rays(), field=sc.field_luneburg, step_res=32)
     grid_case("2 fibre (grid form) 64^3, 512^2", 64, *sc.rays_collimated(512))
     cable_case("2 fibre (cable) 129 samples, 512^2", 129, 512)
     grid_case("3 fuel injection 65^3, 32x64^2x16", 65, *multiview_rays(32, 64, 16))
     grid_case("4 caustic 256^3, 2048^2", 256, *sc.rays_collimated(2048))
     grid_case("4' caustic 256^3, 2048^2 cone .05", 256, *sc.rays_cone(2048, spread=0.05))
+    grid_case("4'' caustic 256^3, 2048^2 cone .15", 256, *sc.rays_cone(2048, spread=0.15))
     grid_case("5 focal stack 512^3, 2M rays/GPU", 512, *sc.rays_collimated(1448))
     grid_case("5' focal stack 512^3, 4096^2", 512, *sc.rays_collimated(4096))
 

@@ -24,17 +24,30 @@ CASES = {
     "fuel": lambda: (65, *multiview_rays(32, 64, 16)),
     "focal": lambda: (512, *sc.rays_collimated(1448)),
     "luneburg": lambda: (32, *sc.rays_collimated(256)),
+    "lunyaml": lambda: (129, *lunyaml()),
 }
+STEP_RES = {"lunyaml": 32}
+
+
+def lunyaml():
+    from adjointnonlinearraytracing_b200 import source
+    torch.manual_seed(0); np.random.seed(0)
+    rot = source.random_rotmat().numpy()
+    (x, v, planes), nr = source.rand_rays_cube((128, 128), 10, 1.0, circle=True, rotmat=rot)
+    return x.cpu().numpy(), v.cpu().numpy()
 
 if __name__ == "__main__":
     name = sys.argv[1]
     flag_list = [int(f, 0) for f in sys.argv[2].split(",")]
     reps = int(sys.argv[3]) if len(sys.argv) > 3 else 1
     ng, pos, vel = CASES[name]()
-    rif = T(sc.field_bump(ng)); h = float(sc.grid_spacing(ng)); ds = h / 2
+    rif = T(sc.field_bump(ng)); h = float(sc.grid_spacing(ng)); ds = h / STEP_RES.get(name, 2)
     pos, vel = T(pos), T(vel)
     one = torch.ones_like(pos)
-    xt, vt = ops.trace(rif, pos, vel, h, ds)
+    st = ops.new_stats(dev)
+    a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+    a.record(); xt, vt = ops.trace(rif, pos, vel, h, ds, stats=st); b.record(); torch.cuda.synchronize()
+    print(f"{name} fwd {a.elapsed_time(b):.3f} ms, {int(st[0])} ray-steps, {pos.shape[0]} rays", flush=True)
     for fl in flag_list:
         for _ in range(reps):
             a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
