@@ -43,8 +43,10 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def workload_host(n_g=NG, sensor=SENSOR):
+def workload_host(n_g=None, sensor=None):
     from adjointnonlinearraytracing_b200 import scenes as sc
+    n_g = NG if n_g is None else n_g
+    sensor = SENSOR if sensor is None else sensor
     rif = sc.field_bump(n_g)
     h = float(sc.grid_spacing(n_g))
     ds = h / 2
@@ -373,7 +375,9 @@ def run_ours(args):
             "config": {
                 "workload": WORKLOAD,
                 "rays_per_gpu": n_rays, "grid": [NG, NG, NG], "parallelism": f"rays-dp{world} + grad allreduce" if world > 1 else "single GPU",
-                "l2": "no explicit flush: per-step working set (rays in/out 302 MB + grid 67 MB + gradient 67 MB) exceeds the 126 MB L2; the 67 MB IOR grid staying L2-resident across the step is the design",
+                "l2": (f"no explicit flush: per-step working set (rays in/out {n_rays * 72 / 1e6:.0f} MB + grid {NG ** 3 * 4 / 1e6:.0f} MB + "
+                       f"gradient {NG ** 3 * 4 / 1e6:.0f} MB) exceeds the 126 MB L2"
+                       + ("; the 67 MB IOR grid staying L2-resident across the step is the design" if NG == 256 else "")),
                 "arithmetic": "exact trajectory (default flags=0): ray path bit-identical to the float32 reference formulas", "ray_steps_fwd": s_f, "ray_steps_adj": s_b,
                 "rays_not_exited": not_exited,
             },
@@ -435,7 +439,16 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--workload", default="caustic256", choices=["caustic256", "focal512"],
+                    help="caustic256 = BASELINE.json's metric configuration (default, the bench line); focal512 = "
+                         "configs[4]: 512^3 grid, 1448^2 = 2.1 M rays per GPU (16.8 M over 8 GPUs), a labelled extra run")
     args = ap.parse_args()
+    if args.workload == "focal512":
+        global NG, SENSOR, METRIC, WORKLOAD
+        NG, SENSOR = 512, 1448
+        METRIC = "fwd+adjoint ray-steps/sec at 512^3 grid"
+        WORKLOAD = (f"focal-512 (BASELINE.json configs[4]): {NG}^3 bump IOR grid, {SENSOR}^2 = {SENSOR * SENSOR} "
+                    "collimated rays per GPU, ds = h/2, seeds dx=dv=1")
     _guard_stdout()
     if args.impl == "reference":
         run_reference_arm(args)
