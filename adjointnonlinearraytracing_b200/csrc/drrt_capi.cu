@@ -8,6 +8,8 @@
 #include <string>
 
 #include "../../include/drrt_b200.h"
+#include <math.h>
+
 #include "drrt_launch.h"
 
 using namespace drrt;
@@ -363,15 +365,19 @@ int drrt_sensor_splat_backward(const float *x, const float *v, const float *e, f
                        dx, dv, de, (cudaStream_t) stream);
 }
 
-int drrt_plane_source_rand(const float *offset, uint64_t seed, const float *view_rot, int nviews, int P0, int P1,
-                           int spp, float width, float sensor_dist, int independent, const float *post_rot,
-                           float post_span, float *x, float *v, float *planes, uint8_t *keep,
-                           drrt_stream_t stream) {
-  if (nviews < 0 || P0 <= 0 || P1 <= 0 || spp <= 0) return fail(DRRT_ERR_INVALID_ARGUMENT, "plane source: bad view / pixel / sample count");
+int drrt_source_rand(int kind, const float *offset, uint64_t seed, const float *view_rot, int nviews, int P0,
+                     int P1, int spp, float width, float sensor_dist, float cone_angle_deg, int independent,
+                     const float *post_rot, float post_span, float *x, float *v, float *planes, uint8_t *keep,
+                     drrt_stream_t stream) {
+  if (kind != DRRT_SOURCE_PLANE && kind != DRRT_SOURCE_POINT && kind != DRRT_SOURCE_CONE)
+    return fail(DRRT_ERR_INVALID_ARGUMENT, "ray source: unknown kind");
+  if (nviews < 0 || P0 <= 0 || P1 <= 0 || spp <= 0) return fail(DRRT_ERR_INVALID_ARGUMENT, "ray source: bad view / pixel / sample count");
   if (nviews == 0) return DRRT_OK;
-  if (!view_rot || !x || !v || !planes) return fail(DRRT_ERR_INVALID_ARGUMENT, "plane source: NULL buffer");
+  if (!view_rot || !x || !v || !planes) return fail(DRRT_ERR_INVALID_ARGUMENT, "ray source: NULL buffer");
   SourceArgs a;
   memset(&a, 0, sizeof a);
+  a.kind = kind;
+  a.cone_cos = (float) cos(0.5 * (double) cone_angle_deg * 3.14159265358979323846 / 180.0);
   a.offset = offset; a.seed = seed; a.P0 = P0; a.P1 = P1; a.spp = spp;
   a.rays_per_view = (int64_t) spp * P0 * P1;
   a.width = width; a.sensor_dist = sensor_dist; a.independent = independent;
@@ -388,7 +394,15 @@ int drrt_plane_source_rand(const float *offset, uint64_t seed, const float *view
     a.keep = keep ? keep + r0 : nullptr;
     g_launches += launch_plane_source(a, (cudaStream_t) stream);
   }
-  return check_launch("plane_source");
+  return check_launch("ray_source");
+}
+
+int drrt_plane_source_rand(const float *offset, uint64_t seed, const float *view_rot, int nviews, int P0, int P1,
+                           int spp, float width, float sensor_dist, int independent, const float *post_rot,
+                           float post_span, float *x, float *v, float *planes, uint8_t *keep,
+                           drrt_stream_t stream) {
+  return drrt_source_rand(DRRT_SOURCE_PLANE, offset, seed, view_rot, nviews, P0, P1, spp, width, sensor_dist, 0.f,
+                          independent, post_rot, post_span, x, v, planes, keep, stream);
 }
 
 int drrt_adam_step(float *n, const float *grad, float *exp_avg, float *exp_avg_sq, int S0, int S1, int S2,

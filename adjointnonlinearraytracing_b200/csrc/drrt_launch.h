@@ -5,6 +5,7 @@
 #include <limits.h>
 #include <stdint.h>
 
+#include "../../include/drrt_b200.h"
 #include "drrt_device.cuh"
 
 #define DRRT_LAYOUT_SOA 1
@@ -89,7 +90,7 @@ int launch_sensor_splat(bool far, const SensorArgs &a, cudaStream_t s);
 int launch_sensor_splat_bwd(bool far, const SensorArgs &a, cudaStream_t s);
 
 // on-device ray generation, drrt_source_kernels.cu
-constexpr int kSourceMaxViews = 32;  // views per launch (their rotations travel as kernel parameters)
+constexpr int kSourceMaxViews = 32;  // kinds: DRRT_SOURCE_* of include/drrt_b200.h  // views per launch (their rotations travel as kernel parameters)
 struct SourceArgs {
   const float *offset;   // device uniforms [total views][2*spp][P0][P1], or NULL -> Philox(seed)
   uint64_t seed;
@@ -97,6 +98,8 @@ struct SourceArgs {
   int P0, P1, spp;
   int64_t rays_per_view;   // spp * P0 * P1
   float width, sensor_dist;
+  int kind;                // DRRT_SOURCE_*
+  float cone_cos;          // cone source: cos(cone_angle / 2)
   int independent;
   int has_post;
   float post_rot[9], post_span;

@@ -3,6 +3,8 @@
 // iteration (reference core/luneburg_opt.py:53-59, core/image_opt.py:44-52).
 //
 //   plane_source3_rand     reference core/source.py:54-69  (jittered pixel grid on a plane)
+//   point_source3_rand     reference core/source.py:72-104 (point source through a jittered pixel grid)
+//   cone_source3_rand      reference core/source.py:186-202 + hatbox_sample :531-545 (uniform cone)
 //   rotate_pts_to_source   reference core/source.py:275-293 (view rotation, launch plane,
 //                                                          sensor plane triple)
 //   rand_rays_in_sphere    reference core/source.py:352-357 (one plane source per view)
@@ -64,25 +66,53 @@ __global__ void __launch_bounds__(256) plane_source_kernel(SourceArgs a) {
     ua = u01(b.x); ub = u01(b.y);
   }
   const float w = a.width;
-  f3 p;
-  p.y = 0.f;
-  if (a.independent) {  // core/source.py:60-63
-    p.x = ua * w - 0.5f * w;
-    p.z = ub * w - 0.5f * w;
-  } else {              // core/source.py:56-57, :65-68
-    p.x = w * ((float) i / (float) a.P0 - 0.5f) + (ua * w) / (float) a.P0;
-    p.z = w * ((float) j / (float) a.P1 - 0.5f) + (ub * w) / (float) a.P1;
-  }
-  if (a.keep) a.keep[r] = sqrtf(p.x * p.x + p.z * p.z) < 0.5f * w ? 1 : 0;  // circle: core/source.py:277-280
   const float *R = a.view_rot + 9 * view;
   const float hw = 0.5f * w;
-  f3 x = rot(R, p);                       // :284
-  f3 v = rot(R, f3{0.f, 1.f, 0.f});       // :285
-  f3 t = rot(R, f3{0.f, 0.f, 1.f});       // :286
-  x.x += hw; x.y += hw; x.z += hw;
-  x.x -= w * v.x * 0.5f; x.y -= w * v.y * 0.5f; x.z -= w * v.z * 0.5f;   // :287
-  const float pd = a.sensor_dist + hw;
-  f3 px = {pd * v.x + hw, pd * v.y + hw, pd * v.z + hw};                 // :290
+  const f3 pn = rot(R, f3{0.f, 1.f, 0.f});  // plane normal = the view's optical axis
+  f3 t = rot(R, f3{0.f, 0.f, 1.f});
+  f3 x, v;
+  float pd = a.sensor_dist + hw;            // plane_x = pd * plane_v + w/2 (:290, :198-199)
+  bool inside = true;
+  if (a.kind == DRRT_SOURCE_PLANE) {
+    f3 p;
+    p.y = 0.f;
+    if (a.independent) {  // core/source.py:60-63
+      p.x = ua * w - 0.5f * w;
+      p.z = ub * w - 0.5f * w;
+    } else {              // core/source.py:56-57, :65-68
+      p.x = w * ((float) i / (float) a.P0 - 0.5f) + (ua * w) / (float) a.P0;
+      p.z = w * ((float) j / (float) a.P1 - 0.5f) + (ub * w) / (float) a.P1;
+    }
+    inside = sqrtf(p.x * p.x + p.z * p.z) < hw;  // circle: core/source.py:277-280
+    x = rot(R, p);                          // :284
+    v = pn;                                 // :285
+    x.x += hw; x.y += hw; x.z += hw;
+    x.x -= w * v.x * 0.5f; x.y -= w * v.y * 0.5f; x.z -= w * v.z * 0.5f;   // :287
+  } else {
+    f3 d;
+    if (a.kind == DRRT_SOURCE_POINT) {      // point_source3_rand, core/source.py:72-104
+      // pixel centres jittered by (u - 0.5) -- not scaled by the pixel size in the reference (:73-79)
+      const float pa = w * (((float) i + 0.5f) / (float) a.P0 - 0.5f) + (ua - 0.5f);
+      const float pb = w * (((float) j + 0.5f) / (float) a.P1 - 0.5f) + (ub - 0.5f);
+      inside = sqrtf(pa * pa + pb * pb) < hw;                       // :81-83
+      const float inv = 1.f / sqrtf(pa * pa + w * w + pb * pb);     // :85-89
+      d = f3{pa * inv, w * inv, pb * inv};
+      pd = a.sensor_dist * w * 0.5f;                                // :101
+    } else {                                // cone_source3_rand + hatbox_sample, :186-202, :531-545
+      const float z = ua * (1.f - a.cone_cos) + a.cone_cos;
+      float sn, cs;
+      sincosf(6.283185307179586f * ub, &sn, &cs);
+      const float sc = sqrtf(fmaxf(1.f - z * z, 0.f));
+      // t1 = (0,0,1) x (0,1,0) = (-1,0,0), t2 = t1 x (0,1,0) = (0,0,-1)
+      d = f3{-cs * sc, z, -sn * sc};
+    }
+    x = rot(R, f3{0.f, -hw, 0.f});
+    x.x += hw; x.y += hw; x.z += hw;
+    v = rot(R, d);
+  }
+  if (a.keep) a.keep[r] = inside ? 1 : 0;
+  f3 px = {pd * pn.x + hw, pd * pn.y + hw, pd * pn.z + hw};
+  f3 pnr = pn;
   if (a.has_post) {  // random_rotate_ic, core/source.py:555-563: rotate about the volume centre span / 2
     const float c = 0.5f * a.post_span;
     f3 d = {x.x - c, x.y - c, x.z - c};
@@ -91,12 +121,13 @@ __global__ void __launch_bounds__(256) plane_source_kernel(SourceArgs a) {
     px = rot(a.post_rot, d); px.x += c; px.y += c; px.z += c;
     v = rot(a.post_rot, v);
     t = rot(a.post_rot, t);
+    pnr = rot(a.post_rot, pn);
   }
   float *ox = a.x + 3 * r, *ov = a.v + 3 * r, *op = a.planes + 9 * r;
   ox[0] = x.x; ox[1] = x.y; ox[2] = x.z;
   ov[0] = v.x; ov[1] = v.y; ov[2] = v.z;
   op[0] = px.x; op[1] = px.y; op[2] = px.z;   // planes[:, 0] sensor origin
-  op[3] = v.x; op[4] = v.y; op[5] = v.z;      // planes[:, 1] sensor normal
+  op[3] = pnr.x; op[4] = pnr.y; op[5] = pnr.z;  // planes[:, 1] sensor normal
   op[6] = t.x; op[7] = t.y; op[8] = t.z;      // planes[:, 2] sensor tangent
 }
 

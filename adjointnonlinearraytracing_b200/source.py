@@ -20,7 +20,8 @@ import torch
 
 from . import _capi
 
-__all__ = ["rotation_matrix", "plane_source3_rand", "rand_rays_in_sphere", "rand_rays_cube",
+__all__ = ["rotation_matrix", "plane_source3_rand", "point_source3_rand", "cone_source3_rand",
+           "rand_rays_in_sphere", "rand_ptrays_in_sphere", "rand_ptcone_in_sphere", "rand_rays_cube",
            "random_rotmat", "random_rotate_ic", "rotate_ray3", "sum_norm"]
 
 
@@ -44,8 +45,11 @@ def _fresh_seed() -> int:
     return int(torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).item())
 
 
+PLANE, POINT, CONE = 0, 1, 2   # DRRT_SOURCE_* of include/drrt_b200.h
+
+
 def _generate(view_mats, pixels, spp, width, circle, sensor_dist, independent, offset, seed, device, post=None,
-              post_span=0.0):
+              post_span=0.0, kind=PLANE, cone_angle=90.0):
     nviews = len(view_mats)
     P0, P1 = int(pixels[0]), int(pixels[1])
     per_view = int(spp) * P0 * P1
@@ -66,10 +70,10 @@ def _generate(view_mats, pixels, spp, width, circle, sensor_dist, independent, o
     mats = np.ascontiguousarray(np.stack(view_mats).astype(np.float32)) if nviews else np.zeros((0, 3, 3), np.float32)
     post_arr = None if post is None else np.ascontiguousarray(np.asarray(post, dtype=np.float32).reshape(9))
     with torch.cuda.device(dev):
-        _capi.check(_capi.load().drrt_plane_source_rand(
-            c_void_p(offset.data_ptr() if offset is not None else 0), ctypes.c_uint64(int(seed or 0)),
+        _capi.check(_capi.load().drrt_source_rand(
+            int(kind), c_void_p(offset.data_ptr() if offset is not None else 0), ctypes.c_uint64(int(seed or 0)),
             mats.ctypes.data_as(c_void_p), nviews, P0, P1, int(spp), float(width), float(sensor_dist),
-            1 if independent else 0,
+            float(cone_angle), 1 if independent else 0,
             post_arr.ctypes.data_as(c_void_p) if post_arr is not None else c_void_p(0), float(post_span),
             c_void_p(x.data_ptr()), c_void_p(v.data_ptr()), c_void_p(planes.data_ptr()),
             c_void_p(keep.data_ptr() if keep is not None else 0),
@@ -90,6 +94,43 @@ def plane_source3_rand(angle, pixels, spp, width, circle=False, xaxis=False, sen
     return x, v, planes
 
 
+def point_source3_rand(angle, pixels, spp, width, circle=False, xaxis=False, sensor_dist=1.0, *, offset=None,
+                       seed=None, device="cuda"):
+    """reference core/source.py:72-104 -> (x, v, planes): rays from one point through a jittered pixel grid."""
+    x, v, planes, _ = _generate([rotation_matrix(angle, xaxis)], pixels, spp, width, circle, sensor_dist, False,
+                                offset, seed, device, kind=POINT)
+    return x, v, planes
+
+
+def cone_source3_rand(angle, pixels, spp, width, circle=False, xaxis=False, sensor_dist=1.0, cone_angle=100.0, *,
+                      offset=None, seed=None, device="cuda"):
+    """reference core/source.py:186-202 (+ hatbox_sample :531-545) -> (x, v, planes): pixels[0]*pixels[1]*spp
+    directions uniform in a cone; `circle` is accepted and ignored, as in the reference."""
+    x, v, planes, _ = _generate([rotation_matrix(angle, xaxis)], pixels, spp, width, False, sensor_dist, False,
+                                offset, seed, device, kind=CONE, cone_angle=cone_angle)
+    return x, v, planes
+
+
+def rand_ptrays_in_sphere(nviews, im_res, spp, width, angle_span=360, circle=False, xaxis=False, sensor_dist=0.0, *,
+                          offset=None, seed=None, device="cuda"):
+    """reference core/source.py:360-365 -> ((x, v, planes), rays_per_view)."""
+    angles = torch.linspace(0, angle_span, nviews + 1)
+    mats = [rotation_matrix(angles[i], xaxis) for i in range(nviews)]
+    x, v, planes, nrays = _generate(mats, im_res, spp, width, circle, sensor_dist, False, offset, seed, device,
+                                    kind=POINT)
+    return (x, v, planes), nrays
+
+
+def rand_ptcone_in_sphere(nviews, im_res, spp, width, angle_span=360, circle=False, xaxis=False, sensor_dist=1.0,
+                          cone_angle=90.0, *, offset=None, seed=None, device="cuda"):
+    """reference core/source.py:388-396 -> ((x, v, planes), dists, rays_per_view); dists = zeros(nviews)."""
+    angles = torch.linspace(0, angle_span, nviews + 1)
+    mats = [rotation_matrix(angles[i], xaxis) for i in range(nviews)]
+    x, v, planes, nrays = _generate(mats, im_res, spp, width, False, sensor_dist, False, offset, seed, device,
+                                    kind=CONE, cone_angle=cone_angle)
+    return (x, v, planes), torch.zeros(nviews), nrays
+
+
 def rand_rays_in_sphere(nviews, im_res, spp, width, angle_span=360, circle=False, xaxis=False, sensor_dist=1.0,
                         indep=False, *, offset=None, seed=None, device="cuda"):
     """reference core/source.py:352-357 -> ((x, v, planes), rays_per_view)."""
@@ -108,13 +149,15 @@ def _cube_views():
 
 def rand_rays_cube(im_res, spp, width, circle=False, src_type="plane", cone_ang=90, *, offset=None, seed=None,
                    device="cuda", rotmat=None):
-    """reference core/source.py:398-412 (plane sources; the point / cone variants are not built).
-    `rotmat` fuses the ``random_rotate_ic`` that always follows in the reference's drivers
-    (core/luneburg_opt.py:54-56) into the same kernel."""
-    if src_type != "plane":
-        raise NotImplementedError("rand_rays_cube: only src_type='plane' is implemented on the device")
-    x, v, planes, nrays = _generate(_cube_views(), im_res, spp, width, circle, 0.0, False, offset, seed, device,
-                                    post=rotmat, post_span=width)
+    """reference core/source.py:398-412: 'plane' -> plane_source3_rand, anything but 'plane' / 'point' ->
+    cone_source3_rand(cone_angle=cone_ang) as in the reference; the regular-lattice 'point' source
+    (point_source3, :29-51) is not built.  `rotmat` fuses the ``random_rotate_ic`` that always follows in
+    the reference's drivers (core/luneburg_opt.py:54-56) into the same kernel."""
+    if src_type == "point":
+        raise NotImplementedError("rand_rays_cube: src_type='point' (point_source3) is not implemented on the device")
+    kind = PLANE if src_type == "plane" else CONE
+    x, v, planes, nrays = _generate(_cube_views(), im_res, spp, width, circle and kind == PLANE, 0.0, False, offset,
+                                    seed, device, post=rotmat, post_span=width, kind=kind, cone_angle=cone_ang)
     return (x, v, planes), nrays
 
 

@@ -248,6 +248,20 @@ int drrt_plane_source_rand(const float *offset, uint64_t seed, const float *view
                            int spp, float width, float sensor_dist, int independent, const float *post_rot,
                            float post_span, float *x, float *v, float *planes, uint8_t *keep,
                            drrt_stream_t stream);
+/* drrt_source_rand: the same call for the other random sources; kind =
+ *   DRRT_SOURCE_PLANE  plane_source3_rand (as above),
+ *   DRRT_SOURCE_POINT  <- source.point_source3_rand (core/source.py:72-104, what
+ *                      rand_ptrays_in_sphere :360-365 concatenates): rays from the point
+ *                      (0,-w/2,0) through a jittered pixel grid; keep = its circle filter,
+ *   DRRT_SOURCE_CONE   <- source.cone_source3_rand + hatbox_sample (:186-202, :531-545, what
+ *                      rand_ptcone_in_sphere :388-396 concatenates): directions uniform in the
+ *                      cone of full angle cone_angle_deg about the view axis; the two uniform
+ *                      planes of `offset` are the reference's z and theta draws. */
+enum { DRRT_SOURCE_PLANE = 0, DRRT_SOURCE_POINT = 1, DRRT_SOURCE_CONE = 2 };
+int drrt_source_rand(int kind, const float *offset, uint64_t seed, const float *view_rot, int nviews, int P0,
+                     int P1, int spp, float width, float sensor_dist, float cone_angle_deg, int independent,
+                     const float *post_rot, float post_span, float *x, float *v, float *planes, uint8_t *keep,
+                     drrt_stream_t stream);
 
 /* ---- host-buffer entry points (what a non-torch binding of the reference API
  * calls; device memory is managed inside the library and cached per thread) --- */

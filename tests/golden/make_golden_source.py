@@ -52,6 +52,20 @@ def main():
     xr, vr, plr = ref_source.random_rotate_ic(x, v, pl, width)
     out["cube_x"] = xr.numpy(); out["cube_v"] = vr.numpy(); out["cube_planes"] = plr.numpy()
     out["cube_nrays"] = np.array(nr); out["cube_offset"] = uniforms(13, 6, spp, pixels); out["cube_rotmat"] = R
+    # point source through a jittered pixel grid, 3 views, circle filter (rand_ptrays_in_sphere)
+    torch.manual_seed(17)
+    (x, v, pl), nr = ref_source.rand_ptrays_in_sphere(3, pixels, spp, width, angle_span=270, circle=True,
+                                                      sensor_dist=0.5)
+    out["pt_x"] = x.numpy(); out["pt_v"] = v.numpy(); out["pt_planes"] = pl.numpy()
+    out["pt_nrays"] = np.array(nr); out["pt_offset"] = uniforms(17, 3, spp, pixels)
+    # cone source, 2 views (rand_ptcone_in_sphere): per view torch.rand(n) for z, then torch.rand(n) for theta
+    torch.manual_seed(19)
+    (x, v, pl), dists, nr = ref_source.rand_ptcone_in_sphere(2, pixels, spp, width, angle_span=180, sensor_dist=0.3,
+                                                             cone_angle=70.0)
+    out["cone_x"] = x.numpy(); out["cone_v"] = v.numpy(); out["cone_planes"] = pl.numpy()
+    n = pixels[0] * pixels[1] * spp
+    torch.manual_seed(19)
+    out["cone_offset"] = np.stack([np.stack([torch.rand(n).numpy(), torch.rand(n).numpy()]) for _ in range(2)])
     out.update(pixels=np.array(pixels), spp=spp, width=width)
     np.savez_compressed(os.path.join(HERE, "source.npz"), **out)
     print("wrote source.npz:", {k: np.shape(a) for k, a in out.items()})
