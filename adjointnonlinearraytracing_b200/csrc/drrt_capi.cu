@@ -350,6 +350,53 @@ int sensor_common(bool backward, const float *x, const float *v, const float *e,
 }
 }  // namespace
 
+namespace {
+int gather_common(bool backward, const float *x, const float *v, int64_t N, int layout, const float *plane_p,
+                  const float *plane_n, const float *t1, const float *t2, const float *tex, int res, float span,
+                  unsigned flags, float *f, const float *df, float *dx, float *dv, cudaStream_t s) {
+  const bool far = (flags & DRRT_SENSOR_FAR) != 0;
+  if (N < 0) return fail(DRRT_ERR_INVALID_ARGUMENT, "negative ray count");
+  if (layout != DRRT_SOA && layout != DRRT_AOS) return fail(DRRT_ERR_INVALID_ARGUMENT, "layout must be DRRT_SOA or DRRT_AOS");
+  if (res <= 0 || !(span > 0.f)) return fail(DRRT_ERR_INVALID_ARGUMENT, "sensor: res and span must be positive");
+  if (!plane_n || !t1 || !t2 || (!far && !plane_p) || !tex) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL plane vector or texture");
+  if (N == 0) return DRRT_OK;
+  if (!v || (!far && !x) || (backward ? !df : !f)) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL ray buffer");
+  SensorArgs a;
+  memset(&a, 0, sizeof a);
+  for (int k = 0; k < 3; ++k) {
+    a.p[k] = plane_p ? plane_p[k] : 0.f; a.n[k] = plane_n[k]; a.t1[k] = t1[k]; a.t2[k] = t2[k];
+  }
+  a.x = x; a.v = v; a.N = N; a.layout = layout; a.res = res;
+  a.offset = 0.5f * span;
+  a.rcp_h = (float) res / span;
+  a.dimage = tex;
+  if (backward) {
+    a.e = df; a.dx = far ? nullptr : dx; a.dv = dv;
+    if (far && dx) CU_TRY(cudaMemsetAsync(dx, 0, sizeof(float) * 3 * (size_t) N, s));
+    g_launches += launch_sensor_gather_bwd(far, a, s);
+  } else {
+    a.de = f;
+    g_launches += launch_sensor_gather(far, a, s);
+  }
+  return check_launch("sensor_gather");
+}
+}  // namespace
+
+int drrt_sensor_gather(const float *x, const float *v, int64_t N, int layout, const float *plane_p,
+                       const float *plane_n, const float *t1, const float *t2, const float *tex, int res,
+                       float span, float *f, unsigned flags, drrt_stream_t stream) {
+  return gather_common(false, x, v, N, layout, plane_p, plane_n, t1, t2, tex, res, span, flags, f, nullptr, nullptr,
+                       nullptr, (cudaStream_t) stream);
+}
+
+int drrt_sensor_gather_backward(const float *x, const float *v, int64_t N, int layout, const float *plane_p,
+                                const float *plane_n, const float *t1, const float *t2, const float *tex, int res,
+                                float span, const float *df, float *dx, float *dv, unsigned flags,
+                                drrt_stream_t stream) {
+  return gather_common(true, x, v, N, layout, plane_p, plane_n, t1, t2, tex, res, span, flags, nullptr, df, dx, dv,
+                       (cudaStream_t) stream);
+}
+
 int drrt_sensor_splat(const float *x, const float *v, const float *e, float e0, int64_t N, int layout,
                       const float *plane_p, const float *plane_n, const float *t1, const float *t2, int res,
                       float span, float *image, unsigned flags, drrt_stream_t stream) {

@@ -88,6 +88,9 @@ struct SensorArgs {
 };
 int launch_sensor_splat(bool far, const SensorArgs &a, cudaStream_t s);
 int launch_sensor_splat_bwd(bool far, const SensorArgs &a, cudaStream_t s);
+// Grid.Get on the plane: texture in a.dimage, per-ray output in a.de (forward); upstream dL/df in a.e (backward)
+int launch_sensor_gather(bool far, const SensorArgs &a, cudaStream_t s);
+int launch_sensor_gather_bwd(bool far, const SensorArgs &a, cudaStream_t s);
 
 // on-device ray generation, drrt_source_kernels.cu
 constexpr int kSourceMaxViews = 32;  // kinds: DRRT_SOURCE_* of include/drrt_b200.h  // views per launch (their rotations travel as kernel parameters)

@@ -38,7 +38,9 @@ struct Proj {
   float vnorm;    // far: |v|
 };
 
-template <bool FAR>
+// NORM: far field only -- project the normalised direction (generate_inf_sensor) or the raw
+// one (get_sdf_vals_far, core/sensor.py:150-151)
+template <bool FAR, bool NORM = true>
 __device__ __forceinline__ Proj project(const SensorArgs &a, f3 x, f3 v, float e) {
   Proj p;
   const f3 n = {a.n[0], a.n[1], a.n[2]}, t1 = {a.t1[0], a.t1[1], a.t1[2]}, t2 = {a.t2[0], a.t2[1], a.t2[2]};
@@ -54,7 +56,7 @@ __device__ __forceinline__ Proj project(const SensorArgs &a, f3 x, f3 v, float e
     p.fs_sign = p.ndv > 0.f ? 1.f : (p.ndv < 0.f ? -1.f : 0.f);
     p.vnorm = 1.f;
   } else {
-    p.vnorm = sqrtf(v.x * v.x + v.y * v.y + v.z * v.z);
+    p.vnorm = NORM ? sqrtf(v.x * v.x + v.y * v.y + v.z * v.z) : 1.f;
     const float r = 1.f / p.vnorm;
     p.ua = (v.x * t1.x + v.y * t1.y + v.z * t1.z) * r + a.offset;
     p.ub = (v.x * t2.x + v.y * t2.y + v.z * t2.z) * r + a.offset;
@@ -126,14 +128,20 @@ __global__ void __launch_bounds__(256) sensor_splat_kernel(SensorArgs a) {
 // Backward of the above for L = sum(dimage * image):
 //   c_k = fe w_k / W;  A = sum_inb G_k w_k;  dL/dnorm = fe (A' W - A W') / W^2 with
 //   w_k' = -d_k / r_k on the support;  dL/dfe = A / W.
-template <bool FAR>
+//
+// GATHER: backward of sensor_gather_kernel instead (Grid.Get, core/grid.py:106-121): the tap
+// values are the texture itself at CLAMPED indices (no bounds mask, core/grid.py:51), the
+// per-ray factor is the upstream gradient dL/df (passed in `e`), and there is no
+// foreshortening term.
+template <bool FAR, bool GATHER>
 __global__ void __launch_bounds__(256) sensor_splat_bwd_kernel(SensorArgs a) {
   const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= a.N) return;
   const f3 x = FAR ? f3{0, 0, 0} : ld3(a.x, r, a.N, a.layout);
   const f3 v = ld3(a.v, r, a.N, a.layout);
   const float e = a.e ? a.e[r] : a.e0;
-  const Proj p = project<FAR>(a, x, v, e);
+  Proj p = project<FAR, !GATHER>(a, x, v, e);
+  if (GATHER) { p.fe = e; p.fs_sign = 0.f; }
   f3 gx = {0, 0, 0}, gv = {0, 0, 0};
   float ge = 0.f;
   if (finite_ray(p)) {
@@ -154,7 +162,11 @@ __global__ void __launch_bounds__(256) sensor_splat_bwd_kernel(SensorArgs a) {
           const float ir = rr > 0.f ? 1.f / rr : 0.f;  // d|d|/dd at 0: torch's subgradient 0
           const float wa = -da * ir, wb = -db * ir;
           Wa += wa; Wb += wb;
-          if (ia >= 0 && ia < a.res && ib >= 0 && ib < a.res) {
+          if (GATHER) {
+            const int ca = min(max(ia, 0), a.res - 1), cb = min(max(ib, 0), a.res - 1);
+            const float G = a.dimage[(size_t) ca * a.res + cb];
+            A = fmaf(G, w, A); Aa = fmaf(G, wa, Aa); Ab = fmaf(G, wb, Ab);
+          } else if (ia >= 0 && ia < a.res && ib >= 0 && ib < a.res) {
             const float G = a.dimage[(size_t) ia * a.res + ib];
             A = fmaf(G, w, A); Aa = fmaf(G, wa, Aa); Ab = fmaf(G, wb, Ab);
           }
@@ -175,6 +187,8 @@ __global__ void __launch_bounds__(256) sensor_splat_bwd_kernel(SensorArgs a) {
       const float f = p.fs_sign * e * AoW;
       gv.x = fmaf(p.t, gx.x, a.n[0] * f); gv.y = fmaf(p.t, gx.y, a.n[1] * f); gv.z = fmaf(p.t, gx.z, a.n[2] * f);
       ge = fabsf(p.ndv) * AoW;
+    } else if (GATHER) {
+      gv = q;  // vn = v . T, no normalisation (core/sensor.py:150)
     } else {
       // vn = (v / |v|) . T:  dL/dv = (q - vhat (vhat.q)) / |v|
       const float iv = 1.f / p.vnorm;
@@ -189,7 +203,51 @@ __global__ void __launch_bounds__(256) sensor_splat_bwd_kernel(SensorArgs a) {
   if (a.de) a.de[r] = ge;
 }
 
+// Grid.Get on the sensor plane: get_sdf_vals_near / get_sdf_vals_far (core/sensor.py:116-155):
+// f = sum_k tex[clamp(idx_k)] w_k / sum_k w_k over the same 4x4 radial-tent stencil.
+template <bool FAR>
+__global__ void __launch_bounds__(256) sensor_gather_kernel(SensorArgs a) {
+  const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= a.N) return;
+  const f3 x = FAR ? f3{0, 0, 0} : ld3(a.x, r, a.N, a.layout);
+  const f3 v = ld3(a.v, r, a.N, a.layout);
+  const Proj p = project<FAR, false>(a, x, v, 1.f);
+  float f = 0.f;
+  if (finite_ray(p)) {
+    const Stencil s = stencil_of(a, p);
+    float w[16];
+    const float W = tap_weights(s, w);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int ca = min(max(s.ia - 1 + i, 0), a.res - 1);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int cb = min(max(s.ib - 1 + j, 0), a.res - 1);
+        if (w[4 * i + j] != 0.f) f = fmaf(a.dimage[(size_t) ca * a.res + cb], w[4 * i + j], f);
+      }
+    }
+    f /= W;
+  }
+  a.de[r] = f;
+}
+
 }  // namespace
+
+int launch_sensor_gather(bool far, const SensorArgs &a, cudaStream_t s) {
+  if (a.N <= 0) return 0;
+  const unsigned nb = (unsigned) ((a.N + 255) / 256);
+  if (far) sensor_gather_kernel<true><<<nb, 256, 0, s>>>(a);
+  else sensor_gather_kernel<false><<<nb, 256, 0, s>>>(a);
+  return 1;
+}
+
+int launch_sensor_gather_bwd(bool far, const SensorArgs &a, cudaStream_t s) {
+  if (a.N <= 0) return 0;
+  const unsigned nb = (unsigned) ((a.N + 255) / 256);
+  if (far) sensor_splat_bwd_kernel<true, true><<<nb, 256, 0, s>>>(a);
+  else sensor_splat_bwd_kernel<false, true><<<nb, 256, 0, s>>>(a);
+  return 1;
+}
 
 int launch_sensor_splat(bool far, const SensorArgs &a, cudaStream_t s) {
   if (a.N <= 0) return 0;
@@ -202,8 +260,8 @@ int launch_sensor_splat(bool far, const SensorArgs &a, cudaStream_t s) {
 int launch_sensor_splat_bwd(bool far, const SensorArgs &a, cudaStream_t s) {
   if (a.N <= 0) return 0;
   const unsigned nb = (unsigned) ((a.N + 255) / 256);
-  if (far) sensor_splat_bwd_kernel<true><<<nb, 256, 0, s>>>(a);
-  else sensor_splat_bwd_kernel<false><<<nb, 256, 0, s>>>(a);
+  if (far) sensor_splat_bwd_kernel<true, false><<<nb, 256, 0, s>>>(a);
+  else sensor_splat_bwd_kernel<false, false><<<nb, 256, 0, s>>>(a);
   return 1;
 }
 

@@ -18,7 +18,8 @@ import torch
 from . import _capi
 from ._capi import DRRT_AOS, DRRT_SENSOR_FAR
 
-__all__ = ["trace_rays_to_plane", "get_tan_vecs", "generate_sensor", "generate_inf_sensor"]
+__all__ = ["trace_rays_to_plane", "get_tan_vecs", "generate_sensor", "generate_inf_sensor",
+           "get_sdf_vals_near", "get_sdf_vals_far"]
 
 
 def trace_rays_to_plane(rays, plane):
@@ -122,3 +123,54 @@ def generate_inf_sensor(rays, e, plane, res, angle_span=120, tangent=None):
     x, v = rays
     ang_cut = math.sin(0.5 * math.radians(angle_span))
     return _SensorSplat.apply(x, v, e, _plane(plane, tangent), res, 2.0 * ang_cut, True)
+
+
+class _SensorGather(torch.autograd.Function):
+    """Grid.Get of a texture at the rays' plane coordinates (drrt_sensor_gather[_backward])."""
+
+    @staticmethod
+    def forward(ctx, x, v, tex, plane, span, far):
+        xd, vd = _rayten(x, "x"), _rayten(v, "v")
+        if tex.dim() != 2 or tex.shape[0] != tex.shape[1] or not tex.is_cuda:
+            raise RuntimeError("d_tex: expected a square 2-D CUDA tensor")
+        td = tex.detach().to(torch.float32).contiguous()
+        N, res = xd.shape[0], int(td.shape[0])
+        ctx.args = (xd, vd, td, plane, res, float(span), DRRT_SENSOR_FAR if far else 0)
+        f = torch.empty(N, dtype=torch.float32, device=xd.device)
+        p, n, t1, t2 = plane
+        with torch.cuda.device(xd.device):
+            s = c_void_p(torch.cuda.current_stream(xd.device).cuda_stream)
+            _capi.check(_capi.load().drrt_sensor_gather(
+                c_void_p(xd.data_ptr()), c_void_p(vd.data_ptr()), N, DRRT_AOS, p, n, t1, t2, c_void_p(td.data_ptr()),
+                res, float(span), c_void_p(f.data_ptr()), ctx.args[6], s))
+        return f
+
+    @staticmethod
+    def backward(ctx, df):
+        xd, vd, td, plane, res, span, flags = ctx.args
+        p, n, t1, t2 = plane
+        N = xd.shape[0]
+        df = df.detach().to(torch.float32).contiguous()
+        need_x, need_v = ctx.needs_input_grad[:2]
+        dx = torch.empty_like(xd) if need_x else None
+        dv = torch.empty_like(vd) if need_v else None
+        with torch.cuda.device(xd.device):
+            s = c_void_p(torch.cuda.current_stream(xd.device).cuda_stream)
+            _capi.check(_capi.load().drrt_sensor_gather_backward(
+                c_void_p(xd.data_ptr()), c_void_p(vd.data_ptr()), N, DRRT_AOS, p, n, t1, t2, c_void_p(td.data_ptr()),
+                res, span, c_void_p(df.data_ptr()), c_void_p(dx.data_ptr() if dx is not None else 0),
+                c_void_p(dv.data_ptr() if dv is not None else 0), flags, s))
+        return dx, dv, None, None, None, None
+
+
+def get_sdf_vals_near(rays, d_tex, plane, span, tangent=None):
+    """reference core/sensor.py:116-134: the texture `d_tex` sampled (Grid.Get) where each ray meets the plane."""
+    x, v = rays
+    return _SensorGather.apply(x, v, d_tex, _plane(plane, tangent), span, False)
+
+
+def get_sdf_vals_far(rays, d_tex, plane, ang_span, tangent=None):
+    """reference core/sensor.py:137-155: the texture sampled at the rays' (raw) direction coordinates."""
+    x, v = rays
+    ang_cut = math.sin(0.5 * math.radians(ang_span))
+    return _SensorGather.apply(x, v, d_tex, _plane(plane, tangent), 2.0 * ang_cut, True)

@@ -230,6 +230,21 @@ int drrt_sensor_splat_backward(const float *x, const float *v, const float *e, f
                                int res, float span, const float *dimage, float *dx, float *dv, float *de,
                                unsigned flags, drrt_stream_t stream);
 
+/* drrt_sensor_gather <- sensor.get_sdf_vals_near (core/sensor.py:116-134) and, with
+ *     DRRT_SENSOR_FAR, sensor.get_sdf_vals_far (:137-155; `span` = 2 sin(angle_span/2), the RAW
+ *     direction is projected, as in the reference): Grid.Get (core/grid.py:106-121) of the
+ *     res x res texture `tex` (device) at each ray's plane coordinates, over the same 4x4
+ *     radial-tent stencil with indices clamped to the texture.  f: N floats.
+ * drrt_sensor_gather_backward <- its torch-autograd backward w.r.t. the rays: given dL/df
+ *     (N floats) writes dL/dx, dL/dv (each nullable). */
+int drrt_sensor_gather(const float *x, const float *v, int64_t N, int layout, const float *plane_p,
+                       const float *plane_n, const float *t1, const float *t2, const float *tex, int res,
+                       float span, float *f, unsigned flags, drrt_stream_t stream);
+int drrt_sensor_gather_backward(const float *x, const float *v, int64_t N, int layout, const float *plane_p,
+                                const float *plane_n, const float *t1, const float *t2, const float *tex, int res,
+                                float span, const float *df, float *dx, float *dv, unsigned flags,
+                                drrt_stream_t stream);
+
 /* ---- on-device ray generation (the step before every trace in the reference's drivers) ----
  * drrt_plane_source_rand <- source.plane_source3_rand + rotate_pts_to_source (reference
  *     core/source.py:54-69, :275-293) for `nviews` views in one call, which is what

@@ -60,6 +60,21 @@ def main():
                                          tangent=torch.tensor(tg))
     (img * torch.tensor(dimg)).sum().backward()
     out["far_image"] = img.detach().numpy(); out["far_dv"] = V.grad.numpy()
+    # texture look-ups (get_sdf_vals_near / _far) and their autograd backward
+    tex = rng.standard_normal((res, res))
+    df = rng.standard_normal(n)
+    X = torch.tensor(x, requires_grad=True); V = torch.tensor(v, requires_grad=True)
+    f = ref_sensor.get_sdf_vals_near((X, V), torch.tensor(tex), (torch.tensor(p), torch.tensor(nn)), span,
+                                     torch.tensor(tg))
+    (f * torch.tensor(df)).sum().backward()
+    out["gnear_f"] = f.detach().numpy(); out["gnear_dx"] = X.grad.numpy(); out["gnear_dv"] = V.grad.numpy()
+    vs = v * 0.4   # keep the raw direction coordinates on the far-field texture
+    X = torch.tensor(x); V = torch.tensor(vs, requires_grad=True)
+    f = ref_sensor.get_sdf_vals_far((X, V), torch.tensor(tex), (torch.tensor(p), torch.tensor(nn)), 60,
+                                    torch.tensor(tg))
+    (f * torch.tensor(df)).sum().backward()
+    out["gfar_f"] = f.detach().numpy(); out["gfar_dv"] = V.grad.numpy(); out["gfar_v"] = vs
+    out.update(tex=tex, df=df)
     out.update(x=x, v=v, e=e, p=p, n=nn, tangent=tg, dimage=dimg, res=res, span=span, far_angle_span=60)
     np.savez_compressed(os.path.join(HERE, "sensor.npz"), **out)
     print("wrote sensor.npz:", {k: np.shape(a) for k, a in out.items()})
