@@ -79,10 +79,11 @@ def _generate(view_mats, pixels, spp, width, circle, sensor_dist, independent, o
             c_void_p(keep.data_ptr() if keep is not None else 0),
             c_void_p(torch.cuda.current_stream(dev).cuda_stream)))
     if circle:
-        m = keep.view(nviews, per_view).bool()
-        counts = m.sum(dim=1).tolist()   # rays per view after the circle filter (the reference's `nrays`)
-        m = m.reshape(-1)
-        return x[m], v[m], planes[m], [int(c) for c in counts]
+        # one host sync (the per-view survivor counts = the reference's `nrays`), then a sync-free
+        # compaction: nonzero_static knows its output size, index_select gathers the three arrays
+        counts = [int(c) for c in keep.view(nviews, per_view).sum(dim=1, dtype=torch.int64).tolist()]
+        idx = torch.nonzero_static(keep, size=sum(counts)).squeeze(1)
+        return x.index_select(0, idx), v.index_select(0, idx), planes.index_select(0, idx), counts
     return x, v, planes, [per_view] * nviews
 
 

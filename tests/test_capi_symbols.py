@@ -42,3 +42,37 @@ def test_no_compute_without_gpu_is_loud():
     rays = torch.zeros(8, 3)
     with pytest.raises(RuntimeError, match="CUDA"):
         ops.trace(rif, rays, rays, 0.25, 0.125)
+
+
+def test_argument_validation_of_the_epilogue_entry_points(cuda_lib):
+    """Bad arguments are rejected before any CUDA call (so this runs without a GPU), with a message."""
+    from ctypes import c_void_p
+    import ctypes as C
+    v3 = (C.c_float * 3)(0, 0, 1)
+    null = c_void_p(0)
+    buf = c_void_p(0x1000)  # never dereferenced: validation fails first
+    lib = cuda_lib
+
+    def err():
+        return lib.drrt_last_error().decode()
+
+    assert lib.drrt_sensor_splat(buf, buf, null, 1.0, 8, 3, v3, v3, v3, v3, 0, 1.0, buf, 0, null) == -1
+    assert "res and span" in err()
+    assert lib.drrt_sensor_splat(buf, buf, null, 1.0, 8, 7, v3, v3, v3, v3, 8, 1.0, buf, 0, null) == -1
+    assert "layout" in err()
+    assert lib.drrt_sensor_splat(buf, buf, null, 1.0, 8, 3, null, v3, v3, v3, 8, 1.0, buf, 0, null) == -1
+    assert lib.drrt_sensor_splat_backward(buf, buf, null, 1.0, 8, 3, v3, v3, v3, v3, 8, 1.0, null, buf, buf, null, 0, null) == -1
+    assert "dimage" in err()
+    assert lib.drrt_sensor_gather(buf, buf, 8, 3, v3, v3, v3, v3, null, 8, 1.0, buf, 0, null) == -1
+    assert lib.drrt_sensor_gather(buf, buf, -1, 3, v3, v3, v3, v3, buf, 8, 1.0, buf, 0, null) == -1
+    assert lib.drrt_source_rand(5, null, 0, buf, 1, 4, 4, 1, 1.0, 0.0, 90.0, 0, null, 0.0, buf, buf, buf, null, null) == -1
+    assert "kind" in err()
+    assert lib.drrt_source_rand(0, null, 0, buf, 1, 0, 4, 1, 1.0, 0.0, 90.0, 0, null, 0.0, buf, buf, buf, null, null) == -1
+    assert lib.drrt_plane_source_rand(null, 0, null, 1, 4, 4, 1, 1.0, 0.0, 0, null, 0.0, buf, buf, buf, null, null) == -1
+    assert lib.drrt_plane_source_rand(null, 0, null, 0, 4, 4, 1, 1.0, 0.0, 0, null, 0.0, null, null, null, null, null) == 0
+    assert lib.drrt_backtrace_rays(buf, null, 4, 4, 4, buf, buf, buf, buf, null, 8, 3, 0.25, 0.125, buf, null, null,
+                                   null, null, 0, null) == -1
+    assert "dpos" in err()
+    assert lib.drrt_backtrace_rays(buf, null, 4, 4, 1, buf, buf, buf, buf, null, 8, 3, 0.25, 0.0, buf, buf, buf,
+                                   null, null, 0, null) < 0
+    assert lib.drrt_adam_step(buf, buf, buf, buf, 4, 4, 4, 0, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, null) == -1
