@@ -368,6 +368,22 @@ def run_ours(args):
                 traffic = json.load(open(tp)).get("backtrace_kernel_dram_bytes_per_launch")
             except Exception:
                 traffic = None
+        # the adjoint's atomics against the MEASURED L2 sector throughput (tools/l2_probe.cu): the grids are
+        # L2-resident at 256^3, so this is the memory roofline the kernel actually lives under
+        l2 = None
+        lp = os.path.join(ROOT, "profiles", "l2_peaks.json")
+        if os.path.exists(lp) and NG == 256:
+            try:
+                pk = json.load(open(lp))
+                red = pk["backtrace_kernel_l1_red_sectors_per_launch"] / (adj_ms * 1e-3) / 1e9
+                ld = pk["backtrace_kernel_l1_ld_sectors_per_launch"] / (adj_ms * 1e-3) / 1e9
+                l2 = {"red_gsectors_per_s": red, "red_peak_gsectors_per_s": pk["red_scattered_gsectors_per_s"],
+                      "red_frac": red / pk["red_scattered_gsectors_per_s"], "gather_gsectors_per_s": ld,
+                      "gather_peak_gsectors_per_s": pk["gather_scattered_gsectors_per_s"],
+                      "note": "sector counts per launch from the committed ncu capture of this workload, divided by the "
+                              "live kernel time; peaks from profiles/r05_l2_probe.log", "source": pk["source"]}
+            except Exception:
+                l2 = None
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
@@ -386,7 +402,7 @@ def run_ours(args):
             "roofline": {
                 "bound": "hbm", "kernel": "backtrace_kernel<sdf=0,A_EXACT,AccumFloat> (face-carry flush, no interleave)", "achieved": adj_gbs, "peak": peak,
                 "unit": "GB/s", "frac": adj_gbs / peak, "traffic": traffic, "peak_source": peak_src,
-                "algorithmic_bytes_per_ray_step": BYTES_ADJ,
+                "algorithmic_bytes_per_ray_step": BYTES_ADJ, "l2": l2,
                 "fwd_kernel": {"achieved": fwd_gbs, "frac": fwd_gbs / peak, "algorithmic_bytes_per_ray_step": BYTES_FWD},
                 "step": {"achieved": (BYTES_FWD * s_f + BYTES_ADJ * s_b) / ((fwd_ms + adj_ms) * 1e-3) / 1e9,
                          "frac": (BYTES_FWD * s_f + BYTES_ADJ * s_b) / ((fwd_ms + adj_ms) * 1e-3) / 1e9 / peak},

@@ -75,3 +75,13 @@ xt, vt = ops.trace(nd, x, v, h, ds)
 print(f"  trace {ev(lambda: ops.trace(nd, x, v, h, ds)):.3f} ms, backtrace {ev(lambda: ops.backtrace(nd, xt, vt, one, one, h, ds)):.3f} ms, "
       f"ray generation {ev(lambda: source.rand_rays_cube((nbins, nbins), spp, span, circle=True)):.3f} ms "
       f"(without the circle compaction {ev(lambda: source.rand_rays_cube((nbins, nbins), spp, span, circle=False)):.3f} ms)")
+
+if os.environ.get("PROFILE") == "1":
+    import cProfile
+    import pstats
+    pr = cProfile.Profile()
+    pr.enable()
+    for _ in range(100):
+        iteration(True)
+    pr.disable()
+    pstats.Stats(pr).sort_stats("cumulative").print_stats(28)
