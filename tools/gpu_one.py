@@ -48,9 +48,13 @@ if __name__ == "__main__":
     a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
     a.record(); xt, vt = ops.trace(rif, pos, vel, h, ds, stats=st); b.record(); torch.cuda.synchronize()
     print(f"{name} fwd {a.elapsed_time(b):.3f} ms, {int(st[0])} ray-steps, {pos.shape[0]} rays", flush=True)
+    g0 = None
     for fl in flag_list:
         for _ in range(reps):
             a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
-            a.record(); ops.backtrace(rif, xt, vt, one, one, h, ds, flags=fl); b.record()
+            a.record(); g = ops.backtrace(rif, xt, vt, one, one, h, ds, flags=fl); b.record()
             torch.cuda.synchronize()
-            print(f"{name} flags={fl:#x} adj {a.elapsed_time(b):.3f} ms", flush=True)
+            if g0 is None:
+                g0 = g.double()
+            err = float((g.double() - g0).norm() / g0.norm())
+            print(f"{name} flags={fl:#x} adj {a.elapsed_time(b):.3f} ms  rel L2 vs first {err:.1e}", flush=True)
