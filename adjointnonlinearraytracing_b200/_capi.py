@@ -61,7 +61,7 @@ PROTOTYPES = {
     "drrt_plane_source_rand": (c_int, [_P, ctypes.c_uint64, _P, _I, _I, _I, _I, _F, _F, _I, _P, _F, _P, _P, _P, _P, _P]),
     "drrt_sensor_gather": (c_int, [_P, _P, _L, _I, _P, _P, _P, _P, _P, _I, _F, _P, _U, _P]),
     "drrt_sensor_gather_backward": (c_int, [_P, _P, _L, _I, _P, _P, _P, _P, _P, _I, _F, _P, _P, _P, _U, _P]),
-    "drrt_source_rand": (c_int, [_I, _P, ctypes.c_uint64, _P, _I, _I, _I, _I, _F, _F, _F, _I, _P, _F, _P, _P, _P, _P, _P]),
+    "drrt_source_rand": (c_int, [_I, _P, ctypes.c_uint64, _P, _I, _I, _I, _I, _F, _F, _F, _I, _P, _F, _P, _P, _P, _P, _P, _P, _P]),
     "drrt_trace_host": (c_int, [_P, _I, _I, _I, _P, _P, _L, _I, _F, _F, _P, _P, _P, _U]),
     "drrt_backtrace_host": (c_int, [_P, _I, _I, _I, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, _U]),
     "drrt_host_cache_grid": (None, [_I]),

@@ -415,8 +415,8 @@ int drrt_sensor_splat_backward(const float *x, const float *v, const float *e, f
 int drrt_source_rand(int kind, const float *offset, uint64_t seed, const float *view_rot, int nviews, int P0,
                      int P1, int spp, float width, float sensor_dist, float cone_angle_deg, int independent,
                      const float *post_rot, float post_span, float *x, float *v, float *planes, uint8_t *keep,
-                     drrt_stream_t stream) {
-  if (kind != DRRT_SOURCE_PLANE && kind != DRRT_SOURCE_POINT && kind != DRRT_SOURCE_CONE)
+                     float *tpv, float *target, drrt_stream_t stream) {
+  if (kind < DRRT_SOURCE_PLANE || kind > DRRT_SOURCE_AREA_BIAS)
     return fail(DRRT_ERR_INVALID_ARGUMENT, "ray source: unknown kind");
   if (nviews < 0 || P0 <= 0 || P1 <= 0 || spp <= 0) return fail(DRRT_ERR_INVALID_ARGUMENT, "ray source: bad view / pixel / sample count");
   if (nviews == 0) return DRRT_OK;
@@ -439,6 +439,8 @@ int drrt_source_rand(int kind, const float *offset, uint64_t seed, const float *
     const size_t r0 = (size_t) first * (size_t) a.rays_per_view;
     a.x = x + 3 * r0; a.v = v + 3 * r0; a.planes = planes + 9 * r0;
     a.keep = keep ? keep + r0 : nullptr;
+    a.tpv = tpv ? tpv + r0 : nullptr;
+    a.target = target ? target + 3 * r0 : nullptr;
     g_launches += launch_plane_source(a, (cudaStream_t) stream);
   }
   return check_launch("ray_source");
@@ -449,7 +451,7 @@ int drrt_plane_source_rand(const float *offset, uint64_t seed, const float *view
                            float post_span, float *x, float *v, float *planes, uint8_t *keep,
                            drrt_stream_t stream) {
   return drrt_source_rand(DRRT_SOURCE_PLANE, offset, seed, view_rot, nviews, P0, P1, spp, width, sensor_dist, 0.f,
-                          independent, post_rot, post_span, x, v, planes, keep, stream);
+                          independent, post_rot, post_span, x, v, planes, keep, nullptr, nullptr, stream);
 }
 
 int drrt_adam_step(float *n, const float *grad, float *exp_avg, float *exp_avg_sq, int S0, int S1, int S2,

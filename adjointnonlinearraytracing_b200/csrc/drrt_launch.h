@@ -109,6 +109,7 @@ struct SourceArgs {
   float view_rot[9 * kSourceMaxViews];
   float *x, *v, *planes;   // outputs of this launch: (n,3), (n,3), (n,3,3)
   uint8_t *keep;           // circle mask of this launch, or NULL
+  float *tpv, *target;     // area sources: per-ray sensor_dist / v.y and target point (n,3); nullable
 };
 int launch_plane_source(const SourceArgs &a, cudaStream_t s);
 

@@ -5,6 +5,8 @@
 //   plane_source3_rand     reference core/source.py:54-69  (jittered pixel grid on a plane)
 //   point_source3_rand     reference core/source.py:72-104 (point source through a jittered pixel grid)
 //   cone_source3_rand      reference core/source.py:186-202 + hatbox_sample :531-545 (uniform cone)
+//   area_source3_cone      reference core/source.py:153-183 (cone per jittered pixel; rand_cone_in_sphere)
+//   area_source3_rand_bias reference core/source.py:107-150 (pixel -> random sensor point; rand_area_in_sphere)
 //   rotate_pts_to_source   reference core/source.py:275-293 (view rotation, launch plane,
 //                                                          sensor plane triple)
 //   rand_rays_in_sphere    reference core/source.py:352-357 (one plane source per view)
@@ -56,14 +58,17 @@ __global__ void __launch_bounds__(256) plane_source_kernel(SourceArgs a) {
   const int64_t q = r - (int64_t) view * a.rays_per_view;  // (s * P0 + i) * P1 + j
   const int j = (int) (q % a.P1);
   const int i = (int) ((q / a.P1) % a.P0);
-  float ua, ub;
-  if (a.offset) {  // torch.rand(2*spp, P0, P1) of this view: [:spp] jitters axis 0, [spp:] axis 1
-    const float *o = a.offset + (int64_t) (a.first_view + view) * 2 * a.rays_per_view;
+  float ua, ub, uc = 0.f, ud = 0.f;
+  const bool area = a.kind == DRRT_SOURCE_AREA_CONE || a.kind == DRRT_SOURCE_AREA_BIAS;
+  if (a.offset) {  // torch.rand(2*spp, P0, P1) of this view: [:spp] jitters axis 0, [spp:] axis 1;
+                   // the area sources draw two more planes per view (rand(n) twice / rand(2, n))
+    const float *o = a.offset + (int64_t) (a.first_view + view) * (area ? 4 : 2) * a.rays_per_view;
     ua = o[q]; ub = o[a.rays_per_view + q];
+    if (area) { uc = o[2 * a.rays_per_view + q]; ud = o[3 * a.rays_per_view + q]; }
   } else {
     const uint4 b = philox4x32_10((uint32_t) q, (uint32_t) (q >> 32), (uint32_t) (a.first_view + view), 0u,
                                   (uint32_t) a.seed, (uint32_t) (a.seed >> 32));
-    ua = u01(b.x); ub = u01(b.y);
+    ua = u01(b.x); ub = u01(b.y); uc = u01(b.z); ud = u01(b.w);
   }
   const float w = a.width;
   const float *R = a.view_rot + 9 * view;
@@ -88,6 +93,42 @@ __global__ void __launch_bounds__(256) plane_source_kernel(SourceArgs a) {
     v = pn;                                 // :285
     x.x += hw; x.y += hw; x.z += hw;
     x.x -= w * v.x * 0.5f; x.y -= w * v.y * 0.5f; x.z -= w * v.z * 0.5f;   // :287
+  } else if (area) {
+    // area_source3_cone (core/source.py:153-183) / area_source3_rand_bias (:107-150): jittered pixel
+    // centres, jitter scaled by width / pixels[0] on BOTH axes (:109, :155)
+    const float js = w / (float) a.P0;
+    const float pa = w * (((float) i + 0.5f) / (float) a.P0 - 0.5f) + (ua - 0.5f) * js;
+    const float pb = w * (((float) j + 0.5f) / (float) a.P1 - 0.5f) + (ub - 0.5f) * js;
+    f3 pos, d, tgt = {0.f, 0.f, 0.f};
+    float tp;
+    if (a.kind == DRRT_SOURCE_AREA_CONE) {
+      pos = f3{pa, -hw, pb};
+      inside = sqrtf(pa * pa + hw * hw + pb * pb) < hw;   // 3-D norm incl. y = -w/2, as written (:163-165)
+      const float z = uc * (1.f - a.cone_cos) + a.cone_cos;  // hatbox_sample about (0,1,0), :531-545
+      float sn, cs;
+      sincosf(6.283185307179586f * ud, &sn, &cs);
+      const float sc = sqrtf(fmaxf(1.f - z * z, 0.f));
+      d = f3{-cs * sc, z, -sn * sc};
+      tp = a.sensor_dist / d.y;                             // :170
+    } else {
+      inside = sqrtf(pa * pa + pb * pb) < hw;               // :118-120
+      tgt = f3{-pa, a.sensor_dist + hw, -pb};               // pt = -pos + (sd + w/2) e_y, :122-124
+      const f3 p0 = {pa, -(a.sensor_dist + hw), pb};        // :123
+      const f3 to = {(uc - 0.5f) * w - p0.x, hw - p0.y, (ud - 0.5f) * w - p0.z};   // :126-133
+      const float inv = 1.f / sqrtf(to.x * to.x + to.y * to.y + to.z * to.z);
+      d = f3{to.x * inv, to.y * inv, to.z * inv};
+      tp = a.sensor_dist / d.y;                             // :136
+      pos = f3{fmaf(tp, d.x, p0.x), fmaf(tp, d.y, p0.y), fmaf(tp, d.z, p0.z)};     // :137
+      tgt = rot(R, tgt); tgt.x += hw; tgt.y += hw; tgt.z += hw;                    // :139
+    }
+    x = rot(R, pos);
+    x.x += hw; x.y += hw; x.z += hw;
+    v = rot(R, d);
+    if (a.tpv) a.tpv[r] = tp;
+    if (a.target) {
+      if (a.has_post) { const float c = 0.5f * a.post_span; tgt = rot(a.post_rot, f3{tgt.x - c, tgt.y - c, tgt.z - c}); tgt.x += c; tgt.y += c; tgt.z += c; }
+      a.target[3 * r] = tgt.x; a.target[3 * r + 1] = tgt.y; a.target[3 * r + 2] = tgt.z;
+    }
   } else {
     f3 d;
     if (a.kind == DRRT_SOURCE_POINT) {      // point_source3_rand, core/source.py:72-104

@@ -21,6 +21,7 @@ import torch
 from . import _capi
 
 __all__ = ["rotation_matrix", "plane_source3_rand", "point_source3_rand", "cone_source3_rand",
+           "area_source3_cone", "area_source3_rand_bias", "rand_cone_in_sphere", "rand_area_in_sphere",
            "rand_rays_in_sphere", "rand_ptrays_in_sphere", "rand_ptcone_in_sphere", "rand_rays_cube",
            "random_rotmat", "random_rotate_ic", "rotate_ray3", "sum_norm"]
 
@@ -45,7 +46,7 @@ def _fresh_seed() -> int:
     return int(torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).item())
 
 
-PLANE, POINT, CONE = 0, 1, 2   # DRRT_SOURCE_* of include/drrt_b200.h
+PLANE, POINT, CONE, AREA_CONE, AREA_BIAS = 0, 1, 2, 3, 4   # DRRT_SOURCE_* of include/drrt_b200.h
 
 
 def _generate(view_mats, pixels, spp, width, circle, sensor_dist, independent, offset, seed, device, post=None,
@@ -61,10 +62,15 @@ def _generate(view_mats, pixels, spp, width, circle, sensor_dist, independent, o
     v = torch.empty((n, 3), dtype=torch.float32, device=dev)
     planes = torch.empty((n, 3, 3), dtype=torch.float32, device=dev)
     keep = torch.empty(n, dtype=torch.uint8, device=dev) if circle else None
+    area = kind in (AREA_CONE, AREA_BIAS)
+    tpv = torch.empty(n, dtype=torch.float32, device=dev) if area else None
+    target = torch.empty((n, 3), dtype=torch.float32, device=dev) if kind == AREA_BIAS else None
+    planes_per_ray = 4 if area else 2
     if offset is not None:
         offset = offset.to(device=dev, dtype=torch.float32).contiguous()
-        if offset.numel() != 2 * n:
-            raise RuntimeError(f"offset: expected {2 * n} uniforms ([views][2*spp][P0][P1]), got {offset.numel()}")
+        if offset.numel() != planes_per_ray * n:
+            raise RuntimeError(f"offset: expected {planes_per_ray * n} uniforms ([views][{planes_per_ray}][spp*P0*P1]), "
+                               f"got {offset.numel()}")
     elif seed is None:
         seed = _fresh_seed()
     mats = np.ascontiguousarray(np.stack(view_mats).astype(np.float32)) if nviews else np.zeros((0, 3, 3), np.float32)
@@ -77,13 +83,20 @@ def _generate(view_mats, pixels, spp, width, circle, sensor_dist, independent, o
             post_arr.ctypes.data_as(c_void_p) if post_arr is not None else c_void_p(0), float(post_span),
             c_void_p(x.data_ptr()), c_void_p(v.data_ptr()), c_void_p(planes.data_ptr()),
             c_void_p(keep.data_ptr() if keep is not None else 0),
+            c_void_p(tpv.data_ptr() if tpv is not None else 0),
+            c_void_p(target.data_ptr() if target is not None else 0),
             c_void_p(torch.cuda.current_stream(dev).cuda_stream)))
     if circle:
         # one host sync (the per-view survivor counts = the reference's `nrays`), then a sync-free
         # compaction: nonzero_static knows its output size, index_select gathers the three arrays
         counts = [int(c) for c in keep.view(nviews, per_view).sum(dim=1, dtype=torch.int64).tolist()]
         idx = torch.nonzero_static(keep, size=sum(counts)).squeeze(1)
-        return x.index_select(0, idx), v.index_select(0, idx), planes.index_select(0, idx), counts
+        out = (x.index_select(0, idx), v.index_select(0, idx), planes.index_select(0, idx), counts)
+        if area:
+            out += (tpv.index_select(0, idx), target.index_select(0, idx) if target is not None else None)
+        return out
+    if area:
+        return x, v, planes, [per_view] * nviews, tpv, target
     return x, v, planes, [per_view] * nviews
 
 
@@ -130,6 +143,44 @@ def rand_ptcone_in_sphere(nviews, im_res, spp, width, angle_span=360, circle=Fal
     x, v, planes, nrays = _generate(mats, im_res, spp, width, False, sensor_dist, False, offset, seed, device,
                                     kind=CONE, cone_angle=cone_angle)
     return (x, v, planes), torch.zeros(nviews), nrays
+
+
+def area_source3_cone(angle, pixels, spp, width, circle=False, xaxis=False, sensor_dist=1.0, cone_angle=90, *,
+                      offset=None, seed=None, device="cuda"):
+    """reference core/source.py:153-183 -> ((x, v, planes), tpv): a cone of directions from every jittered
+    pixel of the launch plane."""
+    x, v, planes, _, tpv, _t = _generate([rotation_matrix(angle, xaxis)], pixels, spp, width, circle, sensor_dist,
+                                         False, offset, seed, device, kind=AREA_CONE, cone_angle=cone_angle)
+    return (x, v, planes), tpv
+
+
+def area_source3_rand_bias(angle, pixels, spp, width, circle=False, xaxis=False, sensor_dist=1.0, *, offset=None,
+                           seed=None, device="cuda"):
+    """reference core/source.py:107-150 -> ((x, v, planes), xt, tpv): each jittered pixel aims at a random
+    point of the sensor."""
+    x, v, planes, _, tpv, xt = _generate([rotation_matrix(angle, xaxis)], pixels, spp, width, circle, sensor_dist,
+                                         False, offset, seed, device, kind=AREA_BIAS)
+    return (x, v, planes), xt, tpv
+
+
+def rand_cone_in_sphere(nviews, im_res, spp, width, angle_span=360, circle=False, xaxis=False, sensor_dist=1.0,
+                        cone_angle=90.0, *, offset=None, seed=None, device="cuda"):
+    """reference core/source.py:379-386 -> ((x, v, planes), tpv, rays_per_view)."""
+    angles = torch.linspace(0, angle_span, nviews + 1)
+    mats = [rotation_matrix(angles[i], xaxis) for i in range(nviews)]
+    x, v, planes, nrays, tpv, _t = _generate(mats, im_res, spp, width, circle, sensor_dist, False, offset, seed,
+                                             device, kind=AREA_CONE, cone_angle=cone_angle)
+    return (x, v, planes), tpv, nrays
+
+
+def rand_area_in_sphere(nviews, im_res, spp, width, angle_span=360, circle=False, xaxis=False, sensor_dist=1.0, *,
+                        offset=None, seed=None, device="cuda"):
+    """reference core/source.py:368-376 -> ((x, v, planes), targets, tpv, rays_per_view)."""
+    angles = torch.linspace(0, angle_span, nviews + 1)
+    mats = [rotation_matrix(angles[i], xaxis) for i in range(nviews)]
+    x, v, planes, nrays, tpv, xt = _generate(mats, im_res, spp, width, circle, sensor_dist, False, offset, seed,
+                                             device, kind=AREA_BIAS)
+    return (x, v, planes), xt, tpv, nrays
 
 
 def rand_rays_in_sphere(nviews, im_res, spp, width, angle_span=360, circle=False, xaxis=False, sensor_dist=1.0,

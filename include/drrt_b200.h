@@ -271,12 +271,21 @@ int drrt_plane_source_rand(const float *offset, uint64_t seed, const float *view
  *   DRRT_SOURCE_CONE   <- source.cone_source3_rand + hatbox_sample (:186-202, :531-545, what
  *                      rand_ptcone_in_sphere :388-396 concatenates): directions uniform in the
  *                      cone of full angle cone_angle_deg about the view axis; the two uniform
- *                      planes of `offset` are the reference's z and theta draws. */
-enum { DRRT_SOURCE_PLANE = 0, DRRT_SOURCE_POINT = 1, DRRT_SOURCE_CONE = 2 };
+ *                      planes of `offset` are the reference's z and theta draws.
+ *   DRRT_SOURCE_AREA_CONE <- source.area_source3_cone (:153-183, what rand_cone_in_sphere :379-386
+ *                      concatenates): a cone of directions from every jittered pixel of the
+ *                      launch plane; DRRT_SOURCE_AREA_BIAS <- source.area_source3_rand_bias
+ *                      (:107-150, rand_area_in_sphere :368-376): each jittered pixel aims at a
+ *                      random point of the sensor.  Both use FOUR uniform planes per view in
+ *                      `offset` ([nviews][4][spp*P0*P1]: the pixel jitter, then the reference's
+ *                      two later draws) and write tpv (N floats: sensor_dist / v.y) and, for
+ *                      AREA_BIAS, target (N x 3: the reference's `xt`); both nullable. */
+enum { DRRT_SOURCE_PLANE = 0, DRRT_SOURCE_POINT = 1, DRRT_SOURCE_CONE = 2, DRRT_SOURCE_AREA_CONE = 3,
+       DRRT_SOURCE_AREA_BIAS = 4 };
 int drrt_source_rand(int kind, const float *offset, uint64_t seed, const float *view_rot, int nviews, int P0,
                      int P1, int spp, float width, float sensor_dist, float cone_angle_deg, int independent,
                      const float *post_rot, float post_span, float *x, float *v, float *planes, uint8_t *keep,
-                     drrt_stream_t stream);
+                     float *tpv, float *target, drrt_stream_t stream);
 
 /* ---- host-buffer entry points (what a non-torch binding of the reference API
  * calls; device memory is managed inside the library and cached per thread) --- */

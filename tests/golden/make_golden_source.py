@@ -66,6 +66,26 @@ def main():
     n = pixels[0] * pixels[1] * spp
     torch.manual_seed(19)
     out["cone_offset"] = np.stack([np.stack([torch.rand(n).numpy(), torch.rand(n).numpy()]) for _ in range(2)])
+    # area sources (circle=False): per view rand(2*spp, P0, P1), then two more planes of n uniforms
+    def uniforms4(seed, nviews, second):
+        torch.manual_seed(seed)
+        res = []
+        for _ in range(nviews):
+            a = torch.rand(2 * spp, *pixels).numpy().reshape(2, -1)
+            b = second()
+            res.append(np.concatenate([a, b]))
+        return np.stack(res)
+
+    torch.manual_seed(23)
+    (x, v, pl), tpv, nr = ref_source.rand_cone_in_sphere(2, pixels, spp, width, angle_span=180, sensor_dist=0.4,
+                                                         cone_angle=50.0)
+    out["acone_x"] = x.numpy(); out["acone_v"] = v.numpy(); out["acone_planes"] = pl.numpy(); out["acone_tpv"] = tpv.numpy()
+    out["acone_offset"] = uniforms4(23, 2, lambda: np.stack([torch.rand(n).numpy(), torch.rand(n).numpy()]))
+    torch.manual_seed(29)
+    (x, v, pl), xt, tpv, nr = ref_source.rand_area_in_sphere(2, pixels, spp, width, angle_span=180, sensor_dist=0.7)
+    out["abias_x"] = x.numpy(); out["abias_v"] = v.numpy(); out["abias_planes"] = pl.numpy()
+    out["abias_xt"] = xt.numpy(); out["abias_tpv"] = tpv.numpy()
+    out["abias_offset"] = uniforms4(29, 2, lambda: torch.rand(2, n).numpy())
     out.update(pixels=np.array(pixels), spp=spp, width=width)
     np.savez_compressed(os.path.join(HERE, "source.npz"), **out)
     print("wrote source.npz:", {k: np.shape(a) for k, a in out.items()})
