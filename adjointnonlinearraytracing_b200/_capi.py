@@ -11,7 +11,8 @@ import os
 from ctypes import POINTER, c_char_p, c_float, c_int, c_int64, c_size_t, c_uint, c_uint8, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libdrrt_b200.so")
+# DRRT_B200_LIB: development override (tuning builds of the same library); unset in production
+LIB_PATH = os.environ.get("DRRT_B200_LIB") or os.path.join(_HERE, "lib", "libdrrt_b200.so")
 
 DRRT_SOA, DRRT_AOS = 1, 3
 DRRT_REFERENCE_ARITH = 1 << 0

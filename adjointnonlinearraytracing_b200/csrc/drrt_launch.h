@@ -19,7 +19,7 @@ constexpr int kAdjThreads = 128;
 #define DRRT_ADJ_MIN_BLOCKS 7
 #endif
 #ifndef DRRT_TRACE_MIN_BLOCKS
-#define DRRT_TRACE_MIN_BLOCKS 9
+#define DRRT_TRACE_MIN_BLOCKS 6  // measured (profiles/r06_tune_occupancy.log): 74 registers / 6 CTAs beat 56 / 9
 #endif
 constexpr int kAdjMinBlocks = DRRT_ADJ_MIN_BLOCKS;
 constexpr int kTraceMinBlocks = DRRT_TRACE_MIN_BLOCKS;
