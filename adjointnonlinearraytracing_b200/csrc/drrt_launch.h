@@ -13,8 +13,14 @@
 
 namespace drrt {
 
-constexpr int kTraceThreads = 128;
-constexpr int kAdjThreads = 128;
+#ifndef DRRT_TRACE_THREADS
+#define DRRT_TRACE_THREADS 128
+#endif
+#ifndef DRRT_ADJ_THREADS
+#define DRRT_ADJ_THREADS 128
+#endif
+constexpr int kTraceThreads = DRRT_TRACE_THREADS;
+constexpr int kAdjThreads = DRRT_ADJ_THREADS;
 #ifndef DRRT_ADJ_MIN_BLOCKS
 #define DRRT_ADJ_MIN_BLOCKS 7
 #endif
