@@ -133,7 +133,13 @@ __global__ void __launch_bounds__(kTraceThreads) trace_cable_kernel(CableArgs a)
 
 // Tracer::backtrace_cable, src/tracer.cpp:511-567, with cylinder_volume::splat
 // (src/cylinder_volume.cpp:113-148) accumulated in shared memory per CTA.
-template <class Accum>
+//
+// REF = false (default): the four splat terms of a step are fused into two (one per sample) and
+// kept in registers while the ray stays between the same two radial samples -- with
+// ds = R / res / 2 along the fibre axis a ray changes its radial bin rarely, and every ray of a CTA
+// hits the same few shared-memory words, so the atomics were the bottleneck (32-way same-address
+// conflicts).  REF = true: the reference's four adds per step, in its order.
+template <class Accum, bool REF>
 __global__ void __launch_bounds__(kAdjThreads) backtrace_cable_kernel(CableArgs a, Accum out_in) {
   typedef typename Accum::T T;
   extern __shared__ unsigned long long smem_raw[];
@@ -155,6 +161,13 @@ __global__ void __launch_bounds__(kAdjThreads) backtrace_cable_kernel(CableArgs 
     mu.x = add_(mu.x, mul_(ds, la.x)); mu.y = add_(mu.y, mul_(ds, la.y)); mu.z = add_(mu.z, mul_(ds, la.z));  // :537
     f3 nv = {-v.x, -v.y, -v.z};
     bool active = !cyl_escaped(c, x, nv);  // :540-541
+    int cur0 = -1, cur1 = -1;   // fused mode: the radial samples the register accumulators belong to
+    float acc0 = 0.f, acc1 = 0.f;
+    auto flush = [&]() {
+      if (cur0 < 0) return;
+      if (use_sm) { atomicAdd(sm + cur0, out.q(acc0)); atomicAdd(sm + cur1, out.q(acc1)); }
+      else { out.add(cur0, acc0); out.add(cur1, acc1); }
+    };
     for (int i = 0; active && i < a.max_steps; ++i) {
       x.x = fma_(-ds, v.x, x.x); x.y = fma_(-ds, v.y, x.y); x.z = fma_(-ds, v.z, x.z);  // :547
       CylCell q = cyl_cell(c, x);
@@ -175,7 +188,13 @@ __global__ void __launch_bounds__(kAdjThreads) backtrace_cable_kernel(CableArgs 
       if (q.r < kCylEps) gv = 0.f;
       float t0 = mul_(val, q.w1), t1 = mul_(val, q.w0);
       float t2 = __fdiv_rn(-gv, c.h), t3 = __fdiv_rn(gv, c.h);
-      if (use_sm) {
+      if (!REF) {
+        if (q.idx0 != cur0 || q.idx1 != cur1) {
+          flush();
+          cur0 = q.idx0; cur1 = q.idx1; acc0 = acc1 = 0.f;
+        }
+        acc0 += t0 + t2; acc1 += t1 + t3;
+      } else if (use_sm) {
         atomicAdd(sm + q.idx0, out.q(t0)); atomicAdd(sm + q.idx1, out.q(t1));
         atomicAdd(sm + q.idx0, out.q(t2)); atomicAdd(sm + q.idx1, out.q(t3));
       } else {
@@ -190,6 +209,7 @@ __global__ void __launch_bounds__(kAdjThreads) backtrace_cable_kernel(CableArgs 
       la.z = add_(la.z, mul_(ds, add_(mul_(dn, nx.z), h2)));
       mu.x = add_(mu.x, mul_(ds, la.x)); mu.y = add_(mu.y, mul_(ds, la.y)); mu.z = add_(mu.z, mul_(ds, la.z));
     }
+    if (!REF) flush();
   }
   if (use_sm) {
     __syncthreads();
@@ -212,17 +232,19 @@ int launch_trace_cable(bool, const CableArgs &a, cudaStream_t s) {
   return 1;
 }
 
-int launch_backtrace_cable(bool, const CableArgs &a, float *grad, unsigned long long *fixed,
+int launch_backtrace_cable(bool ref_arith, const CableArgs &a, float *grad, unsigned long long *fixed,
                            const unsigned *fixed_max_bits, cudaStream_t s) {
   if (a.N <= 0) return 0;
   unsigned nb = blocks_for(a.N, kAdjThreads);
   int n_sm = a.cable.res <= kCableSmemMax ? a.cable.res : 0;
   if (fixed) {
     AccumFixed acc{fixed, fixed_max_bits, 1.0f};
-    backtrace_cable_kernel<AccumFixed><<<nb, kAdjThreads, n_sm * sizeof(unsigned long long), s>>>(a, acc);
+    if (ref_arith) backtrace_cable_kernel<AccumFixed, true><<<nb, kAdjThreads, n_sm * sizeof(unsigned long long), s>>>(a, acc);
+    else backtrace_cable_kernel<AccumFixed, false><<<nb, kAdjThreads, n_sm * sizeof(unsigned long long), s>>>(a, acc);
   } else {
     AccumFloat acc{grad};
-    backtrace_cable_kernel<AccumFloat><<<nb, kAdjThreads, n_sm * sizeof(float), s>>>(a, acc);
+    if (ref_arith) backtrace_cable_kernel<AccumFloat, true><<<nb, kAdjThreads, n_sm * sizeof(float), s>>>(a, acc);
+    else backtrace_cable_kernel<AccumFloat, false><<<nb, kAdjThreads, n_sm * sizeof(float), s>>>(a, acc);
   }
   return 1;
 }

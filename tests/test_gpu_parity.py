@@ -116,9 +116,10 @@ def test_golden_cable(golden, ops, oracle_mod):
     assert np.array_equal(N(xt), xp) and np.array_equal(N(vt), vp) and np.array_equal(N(d2), dp)
     assert np.abs(N(xt) - g["xt"]).max() <= 2e-5 and np.abs(N(vt) - g["vt"]).max() <= 2e-5
     assert np.abs(N(d2) - g["dist2"]).max() <= 2e-5
-    for fl in (0, DET):
+    # default = per-ray register accumulation per radial bin; REF = the reference's four adds per step
+    for fl in (0, DET, REF, REF | DET):
         grad = ops.backtrace_cable(*args, T(g["xt"]), T(g["vt"]), T(g["dx"]), T(g["dv"]), g["ds"], flags=fl)
-        assert rel_l2(N(grad), g["grad"]) <= 1e-4
+        assert rel_l2(N(grad), g["grad"]) <= 1e-4, fl
 
 
 @pytest.mark.parametrize("case", ["probe3", "probe5"])
