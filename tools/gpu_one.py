@@ -25,7 +25,9 @@ CASES = {
     "focal": lambda: (512, *sc.rays_collimated(1448)),
     "luneburg": lambda: (32, *sc.rays_collimated(256)),
     "lunyaml": lambda: (129, *lunyaml()),
+    "lunefield": lambda: (32, *sc.rays_collimated(256)),
 }
+FIELD = {"lunefield": sc.field_luneburg, "lunyaml": sc.field_luneburg}
 STEP_RES = {"lunyaml": 32}
 
 
@@ -41,7 +43,7 @@ if __name__ == "__main__":
     flag_list = [int(f, 0) for f in sys.argv[2].split(",")]
     reps = int(sys.argv[3]) if len(sys.argv) > 3 else 1
     ng, pos, vel = CASES[name]()
-    rif = T(sc.field_bump(ng)); h = float(sc.grid_spacing(ng)); ds = h / STEP_RES.get(name, 2)
+    rif = T(FIELD.get(name, sc.field_bump)(ng)); h = float(sc.grid_spacing(ng)); ds = h / STEP_RES.get(name, 2)
     pos, vel = T(pos), T(vel)
     one = torch.ones_like(pos)
     st = ops.new_stats(dev)
