@@ -12,6 +12,12 @@ of batch k+1 (host->device) and of gradient k-1 (device->host) overlap the kerne
 
 Everything on the device is still the C ABI (``ops.trace`` / ``ops.backtrace`` / the NCCL
 all-reduce); this module only sequences streams and events.
+
+``GraphedStep`` is the other end of the size range: at the reference's small configurations
+(32^3 / 64^3 grids, 65 k - 262 k rays) the two kernels run for 30-300 us, and the step is captured
+once as a CUDA graph and replayed so that the host's launch path (Python marshalling + allocator +
+~6 stream operations) cannot become the bound when the host is busy.  Measured on an idle host the
+gain is 1-2 % (profiles/r09_small_graph.log): even these steps are bound by the kernels.
 """
 from __future__ import annotations
 
@@ -101,3 +107,56 @@ class HostStepPipeline:
     def drain(self):
         for b in range(min(self.k, self.DEPTH)):
             self.ev_out[b].synchronize()
+
+
+class GraphedStep:
+    """``trace -> seed_fn -> backtrace`` over fixed device buffers, captured once as a CUDA graph.
+
+    ``step(pos, vel)`` copies the rays into the captured input buffers (device or pinned host tensors;
+    ``None`` keeps the previous batch), replays the graph and returns ``(xt, vt, grad, stats)`` --
+    views of the captured output buffers, overwritten by the next replay.  ``rif`` is captured by
+    address: in-place updates (``ops.adam_step_``) are seen by the next replay, a re-allocated grid
+    (an up-res level) needs a new ``GraphedStep``.  ``seed_fn`` must be capturable (device-side torch
+    ops only, no ``.item()``); the library's device-pointer entry points never synchronise.
+    """
+
+    def __init__(self, rif: torch.Tensor, h: float, ds: float, n_rays: int, flags: int = 0,
+                 seed_fn: Optional[Callable[[torch.Tensor, torch.Tensor], Tuple[torch.Tensor, torch.Tensor]]] = None,
+                 warmup: int = 2):
+        if not rif.is_cuda or rif.dtype != torch.float32 or not rif.is_contiguous():
+            raise RuntimeError("rif must be a contiguous CUDA float32 tensor (there is no CPU path)")
+        self.rif, self.h, self.ds, self.flags, self.seed_fn = rif, float(h), float(ds), int(flags), seed_fn
+        dev = rif.device
+        self.dev = dev
+        self.pos = torch.zeros(n_rays, 3, device=dev)
+        self.vel = torch.zeros(n_rays, 3, device=dev)
+        self.grad = torch.empty_like(rif)
+        self.stats = ops.new_stats(dev)
+        self.ones = torch.ones(n_rays, 3, device=dev) if seed_fn is None else None
+        self.launches = 0
+        # warm up on a side stream (module load, kernel attributes, allocator pools), then capture
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                self._body()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.xt, self.vt = self._body()
+
+    def _body(self):
+        self.stats.zero_()
+        xt, vt = ops.trace(self.rif, self.pos, self.vel, self.h, self.ds, flags=self.flags, stats=self.stats)
+        dx, dv = (self.ones, self.ones) if self.seed_fn is None else self.seed_fn(xt, vt)
+        ops.backtrace(self.rif, xt, vt, dx, dv, self.h, self.ds, flags=self.flags, stats=self.stats, out=self.grad)
+        return xt, vt
+
+    def step(self, pos: Optional[torch.Tensor] = None, vel: Optional[torch.Tensor] = None):
+        if pos is not None:
+            self.pos.copy_(pos, non_blocking=True)
+        if vel is not None:
+            self.vel.copy_(vel, non_blocking=True)
+        self.graph.replay()
+        self.launches += 1
+        return self.xt, self.vt, self.grad, self.stats

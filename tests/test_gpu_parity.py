@@ -28,6 +28,7 @@ DET = 2  # DRRT_DETERMINISTIC
 FAST = 8  # DRRT_FAST_ARITH
 AGG = 16  # DRRT_WARP_AGGREGATION
 NOIL = 32  # DRRT_NO_INTERLEAVE
+NOFC = 1 << 7  # DRRT_NO_FACE_CARRY
 
 
 @pytest.fixture(scope="module")
@@ -182,6 +183,28 @@ def test_seeded_vs_restatement(ng, s, field, ops, oracle_mod):
     if oracle_mod.ref is not None:  # the reference library itself, when it travelled
         xr, vr = oracle_mod.ref.trace(rif, pos, vel, h, ds)
         endpoint_ok(N(xd), xr); endpoint_ok(N(xt), xr)
+
+
+@pytest.mark.parametrize("step_res", [8, 32])
+def test_fine_steps_many_per_cell(step_res, ops, oracle_mod):
+    """ds = h/8 and h/32 (the reference's Luneburg yaml runs step_res 32): the register cell cache and
+    the face-carry flush hold a cell for dozens of steps; path and gradient still match the restatement."""
+    from adjointnonlinearraytracing_b200 import scenes as sc
+    ng, s = 17, 40
+    rif = sc.field_luneburg(ng)
+    h = sc.grid_spacing(ng); ds = np.float32(h / step_res)
+    pos, vel = sc.rays_cone(s, backoff=0.37 * float(ds))
+    dx, dv = sc.seeds_normal(s * s)
+    xp, vp = oracle_mod.port.trace(rif, pos, vel, h, ds); steps_f = oracle_mod.port.last_steps
+    st = ops.new_stats("cuda")
+    xd, vd = ops.trace(T(rif), T(pos), T(vel), h, ds, stats=st)
+    assert np.array_equal(N(xd), xp) and np.array_equal(N(vd), vp) and int(st[0]) == steps_f
+    gp = oracle_mod.port.backtrace(rif, xp, vp, dx, dv, h, ds); steps_b = oracle_mod.port.last_steps
+    for fl in (REF, 0, NOFC, NOIL, AGG, DET):
+        st = ops.new_stats("cuda")
+        gd = ops.backtrace(T(rif), T(xp), T(vp), T(dx), T(dv), h, ds, flags=fl, stats=st)
+        assert int(st[0]) == steps_b
+        assert rel_l2(N(gd), gp) <= 2e-5 and rel_max(N(gd), gp) <= 2e-4, (fl, rel_l2(N(gd), gp), rel_max(N(gd), gp))
 
 
 def test_noncubic_and_ragged(ops, oracle_mod):

@@ -37,3 +37,33 @@ def test_host_pipeline_matches_direct_calls(cuda_lib):
         ref = ops.backtrace(rif, xt, vt, xt - 0.5, vt, h, ds, flags=DET, stats=stats)
         assert torch.equal(got[k][0], ref.cpu()), k
         assert torch.equal(got[k][1], stats.cpu()), k
+
+
+@pytest.mark.parametrize("flags", [DET, 0])
+def test_graphed_step_replays_what_direct_calls_compute(flags, cuda_lib):
+    """One captured CUDA graph, replayed over new ray batches and an in-place-updated grid."""
+    from adjointnonlinearraytracing_b200 import ops, scenes as sc
+    from adjointnonlinearraytracing_b200.pipeline import GraphedStep
+    ng, s = 33, 64
+    rif = torch.from_numpy(sc.field_noise(ng)).cuda()
+    h = float(sc.grid_spacing(ng)); ds = h / 2
+    seed_fn = lambda xt, vt: (xt - 0.5, vt)
+    step = GraphedStep(rif, h, ds, s * s, flags=flags, seed_fn=seed_fn)
+    for k in range(4):
+        pos, vel = sc.rays_cone(s, seed=k, backoff=0.37 * ds)
+        p, v = torch.from_numpy(pos).pin_memory(), torch.from_numpy(vel).pin_memory()
+        xt, vt, grad, st = step.step(p, v)
+        stats = ops.new_stats("cuda")
+        xr, vr = ops.trace(rif, p.cuda(), v.cuda(), h, ds, flags=flags, stats=stats)
+        ref = ops.backtrace(rif, xr, vr, xr - 0.5, vr, h, ds, flags=flags, stats=stats)
+        assert torch.equal(xt, xr) and torch.equal(vt, vr) and torch.equal(st, stats), k
+        if flags & DET:
+            assert torch.equal(grad, ref), k
+        else:
+            assert float((grad - ref).norm() / ref.norm()) <= 2e-6, k
+        rif.mul_(1.0 + 0.01 * (k + 1)).clamp_(min=1.0)  # the optimiser's in-place update
+    # same batch again (no copy): the updated grid is what the replay reads
+    xt2, vt2, grad2, _ = step.step()
+    xr, vr = ops.trace(rif, p.cuda(), v.cuda(), h, ds, flags=flags)
+    assert torch.equal(xt2, xr) and torch.equal(vt2, vr)
+    assert step.launches == 5
