@@ -24,6 +24,8 @@ DRRT_NO_INTERLEAVE = 1 << 5
 DRRT_SENSOR_FAR = 1 << 6
 DRRT_NO_FACE_CARRY = 1 << 7
 DRRT_AUTO_INTERLEAVE = 1 << 18
+DRRT_NO_REPLICAS = 1 << 19
+DRRT_AGG_RUN_WARP = 15 << 8
 
 
 def DRRT_AGG_RUN(n: int) -> int:

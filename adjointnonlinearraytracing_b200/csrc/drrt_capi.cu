@@ -151,6 +151,24 @@ int trace_common(int kind, const float *rif, const float *sdf, int W, int H, int
   return rc;
 }
 
+// Private gradient copies.  Every float add to ONE address is serialised chip-wide at ~0.7 G adds/s
+// however the adds are packed into requests (profiles/r09_l2_probe_hot.log), so a batch that
+// focuses (a lens) or crosses (tomography views) spends its time queueing on a few voxels.  CTA b
+// therefore adds into copy b % R and one pass sums the copies: R x the throughput on the hot voxels at
+// no cost inside the ray loop.  R is bounded by the copies' footprint (2^23 floats = 32 MiB, L2-
+// resident next to the grid) and by the batch (no more than ~8 rays' worth of voxels to sum).
+// Measured (profiles/r09_replicas.log): Luneburg 32^3 adjoint 332 -> 152 us, 64^3 lens 1234 -> 646 us,
+// fuel-injection views 4.82 -> 4.18 ms, non-focusing 64^3 491 -> 397 us; nothing at 129^3 / 256^3
+// (those are issue-bound, profiles/r09_replicas_big.log), which the footprint bound leaves alone.
+constexpr int kMaxReplicas = 16;
+constexpr int64_t kReplicaFloats = (int64_t) 1 << 23;
+
+int replicas_for_grid(int64_t G, unsigned flags) {
+  if ((flags & (DRRT_DETERMINISTIC | DRRT_NO_REPLICAS)) || G < 4096) return 1;
+  const int64_t r = kReplicaFloats / G;
+  return (int) (r < 1 ? 1 : r > kMaxReplicas ? kMaxReplicas : r);
+}
+
 int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, int H, int D,
                      const float *xt, const float *vt, const float *dx, const float *dv, int64_t N,
                      int layout, float h, float ds, float *grad, void *scratch, int64_t *stats,
@@ -174,6 +192,8 @@ int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, i
   a.N = N; a.layout = layout; a.ds = ds; a.stats = stats;
   a.max_steps = cap_grid(2.0f, h, W, H, D, ds);
   a.agg_policy = (int) ((flags >> 8) & 0xfu);  // experimental: DRRT_AGG_RUN(n), 0 = adaptive
+  if (a.agg_policy == 15) a.agg_policy = 32;   // DRRT_AGG_RUN_WARP
+  a.agg_t8 = 6; a.agg_twarp = 12;  // adaptive policy thresholds (profiles/r09_agg_policies.log)
   a.face_carry = (flags & DRRT_NO_FACE_CARRY) ? 0 : 1;
   unsigned long long *fixed = nullptr;
   unsigned *max_bits = nullptr;
@@ -183,7 +203,17 @@ int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, i
     CU_TRY(cudaMemsetAsync(scratch, 0, sizeof(unsigned long long) * (size_t) G + kFixedTail, s));
     g_launches += launch_fixed_max(dx, dv, 3 * N, max_bits, s);
   }
+  int R = scratch ? replicas_for_grid(G, flags) : 1;
+  if (R > 1) {
+    const int64_t by_rays = 8 * N / G;
+    if (by_rays < R) R = by_rays < 1 ? 1 : (int) by_rays;
+  }
+  if (R > 1) {
+    a.replicas = R; a.replica_base = (float *) scratch; a.replica_stride = G;
+    CU_TRY(cudaMemsetAsync(scratch, 0, sizeof(float) * (size_t) G * (size_t) (R - 1), s));
+  }
   g_launches += launch_backtrace(sdf_kind, arith_of(flags), (flags & DRRT_WARP_AGGREGATION) != 0, interleave_of(flags), a, grad, fixed, max_bits, s);
+  if (R > 1) g_launches += launch_reduce_replicas(grad, (const float *) scratch, G, R - 1, s);
   if (det) g_launches += launch_fixed_to_float(fixed, max_bits, grad, G, accumulate, s);
   return check_launch("backtrace");
 }
@@ -250,8 +280,10 @@ int drrt_trace_cable(const float *rif, int res, float radius, float length, cons
 }
 
 size_t drrt_backtrace_scratch_bytes(int64_t grid_elems, unsigned flags) {
-  if (!(flags & DRRT_DETERMINISTIC) || grid_elems <= 0) return 0;
-  return sizeof(unsigned long long) * (size_t) grid_elems + kFixedTail;
+  if (grid_elems <= 0) return 0;
+  if (flags & DRRT_DETERMINISTIC) return sizeof(unsigned long long) * (size_t) grid_elems + kFixedTail;
+  const int R = replicas_for_grid(grid_elems, flags);
+  return R > 1 ? sizeof(float) * (size_t) grid_elems * (size_t) (R - 1) : 0;
 }
 
 int drrt_backtrace(const float *rif, int W, int H, int D, const float *xt, const float *vt,

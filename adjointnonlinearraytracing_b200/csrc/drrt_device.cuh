@@ -402,6 +402,8 @@ struct AccumFloat {
   typedef float T;
   float *dst;
   __device__ __forceinline__ void prepare() {}
+  // gradient copy `r` of this CTA (0 = dst itself, r >= 1 = copy r - 1 behind `base`)
+  __device__ __forceinline__ void select(int r, float *base, int64_t stride) { if (r) dst = base + (int64_t) (r - 1) * stride; }
   __device__ __forceinline__ float q(float v) const { return v; }
   __device__ __forceinline__ void add(int idx, float v) const { atomicAdd(dst + idx, v); }
 };
@@ -422,6 +424,7 @@ struct AccumFixed {
     return exp2f((float) (34 - e));
   }
   __device__ __forceinline__ void prepare() { scale = scale_from_bits(*max_bits); }
+  __device__ __forceinline__ void select(int, float *, int64_t) {}  // integer sums need no copies
   __device__ __forceinline__ unsigned long long q(float v) const {
     return (unsigned long long) __float2ll_rn(v * scale);
   }

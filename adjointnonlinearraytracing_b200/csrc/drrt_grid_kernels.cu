@@ -272,7 +272,6 @@ __global__ void __launch_bounds__(kTraceThreads) trace_target_tail_kernel(TraceA
 //   9.7 sectors per RED request) disappear.
 // ---------------------------------------------------------------------------
 constexpr unsigned kFull = 0xffffffffu;
-constexpr int kAdapt8 = 24, kAdapt4 = 12, kAdapt2 = 5;  // adaptive policy: average lanes per cell
 constexpr int kAggMin = 4;   // fewer flushing lanes than this: plain atomics
 
 template <class Accum>
@@ -324,13 +323,14 @@ __device__ __forceinline__ void unpack8(const f32x2 P[4], float acc[8]) {
   for (int j = 0; j < 4; ++j) { acc[2 * j] = lo2(P[j]); acc[2 * j + 1] = hi2(P[j]); }
 }
 
-// Segmented shuffle reduction over runs of consecutive flushing lanes that address
-// the same cell, runs cut at multiples of RUN lanes: log2(RUN) rounds of 8 SHFL +
-// 8 FADD.  Returns true on the lane that now holds its run's sum.
+// Segmented shuffle reduction over runs of consecutive lanes that sit in the same cell (lanes
+// that do not flush this step carry zeros, so they do not cut a run), runs cut at multiples of RUN
+// lanes: log2(RUN) rounds of 8 SHFL + 8 FADD.  Returns true on the lane that now holds the sum of
+// a run with at least one flushing lane (`fm` = ballot of the flushing lanes).
 template <int RUN>
-__device__ __forceinline__ bool reduce_runs(float acc[8], bool fl, bool first, unsigned lane) {
-  const bool head = first || (fl && (lane & (RUN - 1)) == 0);
-  const unsigned stops = __ballot_sync(kFull, head || !fl);
+__device__ __forceinline__ bool reduce_runs(float acc[8], bool first, unsigned lane, unsigned fm) {
+  const bool head = first || (lane & (RUN - 1)) == 0;
+  const unsigned stops = __ballot_sync(kFull, head);
   const unsigned above = stops & ~((2u << lane) - 1u);
   const int end = above ? __ffs(above) - 1 : 32;
 #pragma unroll
@@ -342,7 +342,8 @@ __device__ __forceinline__ bool reduce_runs(float acc[8], bool fl, bool first, u
       if (take) acc[k] += t;
     }
   }
-  return head;
+  const unsigned span = (end == 32 ? kFull : (1u << end) - 1u) & ~((1u << lane) - 1u);
+  return head && (fm & span) != 0;
 }
 
 // Per-warp aggregation state: the run length in use and a flush-event counter.
@@ -350,43 +351,49 @@ struct AggState {
   int run, events;
 };
 
-// Warp-uniform: every lane of the warp calls this with its own `fl`.
-// `policy`: 2, 4, 8 = fixed maximum run length; 0 = adaptive.
+// Warp-uniform: every lane of the warp calls this with its own `fl`; `fm` = ballot of `fl` (non-zero).
+// `policy`: 2, 4, 8, 32 = fixed maximum run length; 0 = adaptive.
+// Returns true when the flushing lanes' accumulators were summed and written here, false when the
+// caller should flush each lane on its own (the plain path, with the face carry).
 //
 // Measured (tools/gpu_tune_agg.py, profiles/r03_tune_agg.log): a same-address
 // conflict inside one RED costs less than a shuffle round until ~4 lanes collide,
 // so the best run length is about (lanes per cell) / 4: none at 4 rays per cell,
 // 2 at 8, 4 at 16, 8 at 32.  The adaptive policy re-measures the average number of
 // consecutive lanes per cell every 8th flush of the warp and picks accordingly.
+// The exception is a warp whose flushing lanes ALL sit in one cell (a focused beam): every lane-op on
+// one address is serialised chip-wide at ~0.7 G/s however it is packed into requests
+// (profiles/r09_l2_probe_hot.log), so there the whole warp is summed first (run 32).
 template <class Accum>
-__device__ __forceinline__ void flush_aggregated(const Accum &out, const CellAddr &ca, const f32x2 P[4],
-                                                 bool fl, unsigned lane, int policy, AggState &st) {
-  const unsigned fm = __ballot_sync(kFull, fl);
-  if (fm == 0) return;
-  float acc[8];
-  unpack8(P, acc);
+__device__ __forceinline__ bool flush_aggregated(const Accum &out, const CellAddr &ca, const f32x2 P[4],
+                                                 bool fl, unsigned fm, unsigned lane, int policy, int2 t, AggState &st) {
   const int nfl = __popc(fm);
   const bool probe = policy == 0 && (st.events++ & 7) == 0;
   if (policy != 0) st.run = policy;
-  if ((st.run == 1 && !probe) || nfl < kAggMin) {
-    if (fl) flush_direct(out, ca, acc);
-    return;
-  }
+  if ((st.run == 1 && !probe) || nfl < kAggMin) return false;
   // two lanes address the same 8 voxels iff corner 0 and corner 7 coincide
-  const int k0 = fl ? ca.base : -1;
+  const int k0 = ca.base;
   const int k7 = ca.base + ca.dx + ca.dy + ca.dz;
   const int p0 = __shfl_up_sync(kFull, k0, 1), p7 = __shfl_up_sync(kFull, k7, 1);
-  const bool first = fl && (lane == 0 || p0 != k0 || p7 != k7);  // first lane of a same-cell run
+  const bool first = lane == 0 || p0 != k0 || p7 != k7;  // first lane of a same-cell run
   if (probe) {
     const int nruns = __popc(__ballot_sync(kFull, first));
-    st.run = (nfl >= kAdapt8 * nruns) ? 8 : (nfl >= kAdapt4 * nruns) ? 4 : (nfl >= kAdapt2 * nruns) ? 2 : 1;
+    st.run = (nfl >= t.y * nruns) ? 32 : (nfl >= t.x * nruns) ? 8 : 1;
+    if (st.run == 1) return false;
+  }
+  float acc[8];
+  unpack8(P, acc);
+  if (!fl) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
   }
   bool head;
-  if (st.run == 8) head = reduce_runs<8>(acc, fl, first, lane);
-  else if (st.run == 4) head = reduce_runs<4>(acc, fl, first, lane);
-  else if (st.run == 2) head = reduce_runs<2>(acc, fl, first, lane);
-  else head = fl;
+  if (st.run == 32) head = reduce_runs<32>(acc, first, lane, fm);
+  else if (st.run == 8) head = reduce_runs<8>(acc, first, lane, fm);
+  else if (st.run == 4) head = reduce_runs<4>(acc, first, lane, fm);
+  else head = reduce_runs<2>(acc, first, lane, fm);
   if (head) flush_direct(out, ca, acc);
+  return true;
 }
 
 // ---------------------------------------------------------------------------
@@ -442,11 +449,12 @@ __global__ void __launch_bounds__(256) estimate_interleave_kernel(GridP g, const
 // launch position and the last processed sample (k = 0 when `pos0` is not given, which
 // is exact for rays launched on the first in-bounds sample).
 template <bool SDF, int AR, class Accum, bool AGG, bool RG = false>
-__global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : kAdjMinBlocks) backtrace_kernel(AdjArgs a, Accum out_in) {
+__global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : AGG ? kAdjMinBlocks - 1 : kAdjMinBlocks) backtrace_kernel(AdjArgs a, Accum out_in) {
   constexpr bool REF = AR == A_REF;     // literal 16-atomic splat and lambda/mu order
   constexpr bool TRAJ_REF = AR != A_FAST;
   Accum out = out_in;
   out.prepare();
+  if (a.replicas > 1) out.select((int) (blockIdx.x % (unsigned) a.replicas), a.replica_base, a.replica_stride);
   const unsigned lane = threadIdx.x & 31;
   int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
   if (a.interleave_log2) {  // see "Ray interleaving" above
@@ -502,10 +510,16 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : 
     if (chg) nca = cc.refill(g, c);
     if (!REF) {
       const bool fl = have && (chg || !active);
+      bool summed = false;  // AGG: the warp summed and wrote this flush
       if (AGG) {
-        flush_aggregated(out, ca, P, fl, lane, a.agg_policy, agg);
-      } else if (fl) {
-        if (a.face_carry && active) {  // active && fl implies chg: the ray moves on to cell nca
+        const unsigned fm = __ballot_sync(kFull, fl);
+        if (fm) summed = flush_aggregated(out, ca, P, fl, fm, lane, a.agg_policy, make_int2(a.agg_t8, a.agg_twarp), agg);
+      }
+      if (fl) {
+        if (summed) {
+          P[0] = P[1] = P[2] = P[3] = 0ull;
+          have = false;
+        } else if (a.face_carry && active) {  // active && fl implies chg: the ray moves on to cell nca
           have = flush_carry(out, ca, nca, P);
         } else {
           float acc[8];
@@ -514,10 +528,6 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : 
           P[0] = P[1] = P[2] = P[3] = 0ull;
           have = false;
         }
-      }
-      if (AGG && fl) {
-        P[0] = P[1] = P[2] = P[3] = 0ull;
-        have = false;
       }
     }
     ca = nca;
@@ -572,9 +582,12 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : 
     }
   }
   if (!REF) {
+    bool summed = false;
     if (AGG) {
-      flush_aggregated(out, ca, P, have, lane, a.agg_policy, agg);
-    } else if (have) {
+      const unsigned fm = __ballot_sync(kFull, have);
+      if (fm) summed = flush_aggregated(out, ca, P, have, fm, lane, a.agg_policy, make_int2(a.agg_t8, a.agg_twarp), agg);
+    }
+    if (have && !summed) {
       float acc[8];
       unpack8(P, acc);
       flush_direct(out, ca, acc);
@@ -606,10 +619,11 @@ static inline unsigned blocks_for(int64_t n, int threads) { return (unsigned) ((
 
 template <int KIND>
 static void launch_trace_kind(int arith, const TraceArgs &a, cudaStream_t s) {
-  unsigned nb = blocks_for(a.N, kTraceThreads);
+  const int nt = kTraceThreads;  // 32 / 64 / 128 threads per CTA time the same, also below one wave (profiles/r09_cta_size.log)
+  unsigned nb = blocks_for(a.N, nt);
   // the forward pass is all trajectory: A_EXACT and A_REF are the same kernel
-  if (arith == A_FAST) trace_kernel<KIND, A_FAST><<<nb, kTraceThreads, 0, s>>>(a);
-  else trace_kernel<KIND, A_REF><<<nb, kTraceThreads, 0, s>>>(a);
+  if (arith == A_FAST) trace_kernel<KIND, A_FAST><<<nb, nt, 0, s>>>(a);
+  else trace_kernel<KIND, A_REF><<<nb, nt, 0, s>>>(a);
 }
 
 int launch_trace(int kind, int arith, const TraceArgs &a, cudaStream_t s) {
@@ -631,16 +645,17 @@ static void launch_backtrace_acc(int arith, const AdjArgs &a, Accum acc, cudaStr
   // with interleaving the thread count is rounded up to whole tiles of the largest interleave
   const int64_t tile = 32 * kInterleaveMax;
   const int64_t nthreads = a.interleave_log2 ? ((a.N + tile - 1) / tile) * tile : a.N;
-  unsigned nb = blocks_for(nthreads, kAdjThreads);
+  const int nt = kAdjThreads;
+  unsigned nb = blocks_for(nthreads, nt);
   if (a.dpos) {  // ray gradients: no warp aggregation variant
-    if (arith == A_REF) backtrace_kernel<SDF, A_REF, Accum, false, true><<<nb, kAdjThreads, 0, s>>>(a, acc);
-    else if (arith == A_FAST) backtrace_kernel<SDF, A_FAST, Accum, false, true><<<nb, kAdjThreads, 0, s>>>(a, acc);
-    else backtrace_kernel<SDF, A_EXACT, Accum, false, true><<<nb, kAdjThreads, 0, s>>>(a, acc);
+    if (arith == A_REF) backtrace_kernel<SDF, A_REF, Accum, false, true><<<nb, nt, 0, s>>>(a, acc);
+    else if (arith == A_FAST) backtrace_kernel<SDF, A_FAST, Accum, false, true><<<nb, nt, 0, s>>>(a, acc);
+    else backtrace_kernel<SDF, A_EXACT, Accum, false, true><<<nb, nt, 0, s>>>(a, acc);
     return;
   }
-  if (arith == A_REF) backtrace_kernel<SDF, A_REF, Accum, false><<<nb, kAdjThreads, 0, s>>>(a, acc);
-  else if (arith == A_FAST) backtrace_kernel<SDF, A_FAST, Accum, AGG><<<nb, kAdjThreads, 0, s>>>(a, acc);
-  else backtrace_kernel<SDF, A_EXACT, Accum, AGG><<<nb, kAdjThreads, 0, s>>>(a, acc);
+  if (arith == A_REF) backtrace_kernel<SDF, A_REF, Accum, false><<<nb, nt, 0, s>>>(a, acc);
+  else if (arith == A_FAST) backtrace_kernel<SDF, A_FAST, Accum, AGG><<<nb, nt, 0, s>>>(a, acc);
+  else backtrace_kernel<SDF, A_EXACT, Accum, AGG><<<nb, nt, 0, s>>>(a, acc);
 }
 
 int launch_backtrace(bool sdf, int arith, bool warp_agg, int interleave, const AdjArgs &a_in, float *grad,

@@ -56,8 +56,12 @@ struct AdjArgs {
   int layout;
   float ds;
   int max_steps;
-  int agg_policy;  // warp aggregation: 0 adaptive, 2/4/8 fixed maximum run length
+  int agg_policy;  // warp aggregation: 0 adaptive, 1 off, 2/4/8/32 fixed maximum run length
+  int agg_t8, agg_twarp;  // adaptive: lanes per cell from which runs of 8 / the whole warp are summed
   int face_carry;  // keep the accumulators of the face shared with the next cell in registers
+  int replicas;    // > 1: CTA b adds into gradient copy b % replicas (copy 0 = grad, the others in `replica_base`)
+  float *replica_base;
+  int64_t replica_stride;  // floats per copy (= W*H*D)
   const int *interleave_log2;  // device: log2 of the ray interleave, or NULL (identity mapping)
   int64_t *stats;
   // ray gradients: dL/dpos, dL/dvel of the launch state; pos0 nullable
@@ -133,6 +137,7 @@ int launch_backtrace_cable(bool ref_arith, const CableArgs &a, float *grad,
 // deterministic mode helpers
 int launch_fixed_max(const float *dx, const float *dv, int64_t n3, unsigned *max_bits,
                      cudaStream_t s);
+int launch_reduce_replicas(float *grad, const float *replicas, int64_t G, int extra, cudaStream_t s);
 int launch_fixed_to_float(const unsigned long long *fixed, const unsigned *max_bits, float *grad,
                           int64_t G, bool accumulate, cudaStream_t s);
 

@@ -38,6 +38,24 @@ int launch_fixed_max(const float *dx, const float *dv, int64_t n3, unsigned *max
   return 1;
 }
 
+// grad[i] += sum of the `extra` private copies (the adjoint's per-CTA gradient copies)
+__global__ void __launch_bounds__(256) reduce_replicas_kernel(float *__restrict__ grad, const float *__restrict__ rep,
+                                                              int64_t G, int extra) {
+  for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < G; i += (int64_t) gridDim.x * blockDim.x) {
+    float sum = grad[i];
+    for (int r = 0; r < extra; ++r) sum += rep[(int64_t) r * G + i];
+    grad[i] = sum;
+  }
+}
+
+int launch_reduce_replicas(float *grad, const float *replicas, int64_t G, int extra, cudaStream_t s) {
+  if (G <= 0 || extra <= 0) return 0;
+  int nb = (int) ((G + 255) / 256);
+  if (nb > 148 * 8) nb = 148 * 8;
+  reduce_replicas_kernel<<<nb, 256, 0, s>>>(grad, replicas, G, extra);
+  return 1;
+}
+
 int launch_fixed_to_float(const unsigned long long *fixed, const unsigned *max_bits, float *grad,
                           int64_t G, bool accumulate, cudaStream_t s) {
   if (G <= 0) return 0;

@@ -73,8 +73,9 @@ enum {
    * the lanes of a warp into different cells.
    * DRRT_WARP_AGGREGATION: pre-sum lanes that flush the same cell with a segmented
    * shuffle reduction before the atomics (the alternative to interleaving).
-   * bits 8-11  DRRT_AGG_RUN(n), n in {2,4,8}: fixed maximum run length for the
-   *            aggregation; 0 = adaptive.
+   * bits 8-11  DRRT_AGG_RUN(n), n in {2,4,8} or DRRT_AGG_RUN_WARP: fixed maximum run
+   *            length for the aggregation; 0 = adaptive (whole warp when all flushing
+   *            lanes sit in one cell -- focused beams).
    * bits 12-17 DRRT_INTERLEAVE(n), n in {1,2,4,8,16,32}: fixed interleave; 0 = measured. */
   DRRT_NO_WARP_AGGREGATION = 0u, /* kept for source compatibility: aggregation is opt-in */
   DRRT_WARP_AGGREGATION = 1u << 4,
@@ -84,6 +85,9 @@ enum {
    * also restores the device-measured interleave as the default, i.e. the r03/r04 kernel).
    * DRRT_AUTO_INTERLEAVE: measure the interleave on the device even with the face carry. */
   DRRT_NO_FACE_CARRY = 1u << 7,
+  /* DRRT_NO_REPLICAS: one gradient grid for all CTAs even where the library would use private
+   * copies (grids up to 2^23 / 2 voxels; see drrt_backtrace_scratch_bytes). */
+  DRRT_NO_REPLICAS = 1u << 19,
   DRRT_AUTO_INTERLEAVE = 1u << 18,
   /* Adjoint only: accumulate the gradient in 64-bit fixed point so the result is
    * bit-stable from run to run regardless of atomic ordering (and of the ray
@@ -96,6 +100,7 @@ enum {
 };
 
 #define DRRT_AGG_RUN(n) ((unsigned) (n) << 8)
+#define DRRT_AGG_RUN_WARP (15u << 8)
 #define DRRT_INTERLEAVE(n) ((unsigned) (n) << 12)
 
 int drrt_abi_version(void);
@@ -137,8 +142,12 @@ int drrt_trace_cable(const float *rif, int res, float radius, float length, cons
  * drrt_backtrace       <- TracerC.backtrace       (src/drrt.cpp:56, src/tracer.cpp:384-440)
  * drrt_backtrace_sdf   <- TracerC.backtrace_sdf   (src/drrt.cpp:57, src/tracer.cpp:443-509)
  * drrt_backtrace_cable <- TracerC.backtrace_cable (src/drrt.cpp:58, src/tracer.cpp:511-567)
- * `grad` has W*H*D (resp. `res`) floats.  DRRT_DETERMINISTIC needs `scratch`:
- * a device buffer of drrt_backtrace_scratch_bytes(...) bytes (NULL otherwise).
+ * `grad` has W*H*D (resp. `res`) floats.  `scratch`: a device buffer of
+ * drrt_backtrace_scratch_bytes(grid_elems, flags) bytes, or NULL when that is 0.
+ * DRRT_DETERMINISTIC needs it (the int64 grid).  Without that flag it holds the private
+ * gradient copies of small grids (CTA b adds into copy b % R, one pass sums them: R x
+ * the atomic throughput on the voxels where a focused or crossing batch piles up);
+ * passing NULL there is allowed and simply means one copy.
  */
 size_t drrt_backtrace_scratch_bytes(int64_t grid_elems, unsigned flags);
 

@@ -77,3 +77,20 @@ def test_argument_validation_of_the_epilogue_entry_points(cuda_lib):
     assert lib.drrt_backtrace_rays(buf, null, 4, 4, 1, buf, buf, buf, buf, null, 8, 3, 0.25, 0.0, buf, buf, buf,
                                    null, null, 0, null) < 0
     assert lib.drrt_adam_step(buf, buf, buf, buf, 4, 4, 4, 0, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, null) == -1
+
+
+def test_scratch_bytes_contract(cuda_lib):
+    """drrt_backtrace_scratch_bytes: the int64 grid in deterministic mode, the private gradient copies of
+    small grids otherwise (at most 16 copies and 2^23 floats in total), nothing for large grids."""
+    DET, NOREP = 2, 1 << 19
+    f = cuda_lib.drrt_backtrace_scratch_bytes
+    assert f(0, 0) == 0 and f(-5, DET) == 0
+    assert f(32 ** 3, 0) == 15 * 4 * 32 ** 3          # 16 copies, one of them `grad` itself
+    assert f(65 ** 3, 0) == 15 * 4 * 65 ** 3
+    assert f(128 ** 3, 0) == 3 * 4 * 128 ** 3         # 2^23 / 2^21 = 4 copies
+    assert f(129 ** 3, 0) == 2 * 4 * 129 ** 3
+    assert f(256 ** 3, 0) == 0 and f(512 ** 3, 0) == 0
+    assert f(9 ** 3, 0) == 0 and f(129, 0) == 0       # tiny grids and the cable's radial profile
+    assert f(32 ** 3, NOREP) == 0
+    assert f(32 ** 3, DET) >= 8 * 32 ** 3 and f(32 ** 3, DET) == f(32 ** 3, DET | NOREP)
+    assert f(256 ** 3, DET) >= 8 * 256 ** 3

@@ -6,7 +6,7 @@ import torch
 from conftest import rel_l2
 
 pytestmark = pytest.mark.gpu
-REF, DET, FAST, AGG, NOIL = 1, 2, 8, 16, 32
+REF, DET, FAST, AGG, NOIL, NOFC = 1, 2, 8, 16, 32, 1 << 7
 
 
 @pytest.fixture(scope="module")
@@ -163,8 +163,9 @@ def test_interleave_and_aggregation_only_change_the_summation_order(cuda_lib):
     assert torch.equal(ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=DET | NOFC), base_nofc)
     assert torch.equal(ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=DET | NOFC | IL(8)), base_nofc)
     assert rel_l2(base_nofc.cpu().numpy(), base.cpu().numpy()) <= 2e-6
+    NOREP, WARP = 1 << 19, 15 << 8  # DRRT_NO_REPLICAS, DRRT_AGG_RUN_WARP
     for fl in (0, NOIL, AUTO, NOFC, NOFC | NOIL, AGG, AGG | NOIL, IL(8), IL(32), AGG | (8 << 8) | NOIL,
-               AGG | (2 << 8) | NOIL):
+               AGG | (2 << 8) | NOIL, NOREP, NOREP | AGG, AGG | WARP, NOREP | AGG | WARP, NOREP | NOFC):
         gf = ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=fl)
         assert rel_l2(gf.cpu().numpy(), base.cpu().numpy()) <= 2e-6, fl
 
@@ -199,3 +200,50 @@ def test_face_carry_along_every_axis(axis, sign, cuda_lib, oracle_mod):
     assert rel_l2(g_carry.cpu().numpy(), g_ref) <= 1e-5
     # most rays must actually have crossed the volume
     assert float((xt - torch.from_numpy(pos).cuda()).norm(dim=1).median()) > 0.8
+
+
+@pytest.mark.parametrize("field", ["luneburg", "bump"])
+def test_private_gradient_copies_only_change_the_summation_order(field, cuda_lib):
+    """Small grids: CTA b adds into gradient copy b % R and one pass sums the copies (the scratch buffer of
+    drrt_backtrace_scratch_bytes).  Same gradient as one grid (float rounding) and as the integer mode;
+    DRRT_ACCUMULATE keeps what `out` held; a NULL scratch simply means one copy."""
+    from ctypes import c_void_p
+    from adjointnonlinearraytracing_b200 import _capi, ops, scenes as sc
+    NOREP, ACC = 1 << 19, 4
+    ng, s = 32, 256
+    rif = torch.from_numpy(getattr(sc, "field_" + field)(ng)).cuda()
+    h = float(sc.grid_spacing(ng)); ds = h / 2
+    pos, vel = sc.rays_collimated(s)
+    pos, vel = torch.from_numpy(pos).cuda(), torch.from_numpy(vel).cuda()
+    xt, vt = ops.trace(rif, pos, vel, h, ds)
+    g = torch.Generator(device="cuda").manual_seed(7)
+    dx = torch.randn(s * s, 3, device="cuda", generator=g); dv = torch.randn(s * s, 3, device="cuda", generator=g)
+    lib = _capi.load()
+    G = rif.numel()
+    assert lib.drrt_backtrace_scratch_bytes(G, 0) == 15 * 4 * G and lib.drrt_backtrace_scratch_bytes(G, NOREP) == 0
+    st = ops.new_stats("cuda")
+    det = ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=DET, stats=st)
+    steps = int(st[0])
+    for fl in (0, NOREP, REF, REF | NOREP, AGG, NOFC):
+        st = ops.new_stats("cuda")
+        gr = ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=fl, stats=st)
+        assert int(st[0]) == steps
+        assert rel_l2(gr.cpu().numpy(), det.cpu().numpy()) <= 1e-5, fl
+    # accumulate on top of an existing gradient
+    pre = torch.rand_like(rif)
+    acc = pre.clone()
+    ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=ACC, out=acc)
+    assert rel_l2((acc - pre).cpu().numpy(), det.cpu().numpy()) <= 1e-5
+    # straight through the C ABI with scratch = NULL: allowed, one copy
+    out = torch.full_like(rif, 7.0)
+    P = lambda t: c_void_p(t.data_ptr())
+    rc = lib.drrt_backtrace(P(rif), ng, ng, ng, P(xt), P(vt), P(dx), P(dv), s * s, 3, h, ds, P(out), c_void_p(0),
+                            c_void_p(0), 0, c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    assert rel_l2(out.cpu().numpy(), det.cpu().numpy()) <= 1e-5
+    # few rays on the same grid: fewer copies (8 N / G), still the same answer
+    few = slice(0, 3000)
+    a = ops.backtrace(rif, xt[few].contiguous(), vt[few].contiguous(), dx[few].contiguous(), dv[few].contiguous(), h, ds)
+    b = ops.backtrace(rif, xt[few].contiguous(), vt[few].contiguous(), dx[few].contiguous(), dv[few].contiguous(), h, ds,
+                      flags=DET)
+    assert rel_l2(a.cpu().numpy(), b.cpu().numpy()) <= 1e-5
