@@ -28,6 +28,10 @@ DRRT_NO_REPLICAS = 1 << 19
 DRRT_AGG_RUN_WARP = 15 << 8
 
 
+def DRRT_REPLICAS(n: int) -> int:
+    return int(n) << 20
+
+
 def DRRT_AGG_RUN(n: int) -> int:
     return int(n) << 8
 

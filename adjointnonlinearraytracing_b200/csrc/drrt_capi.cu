@@ -165,6 +165,8 @@ constexpr int64_t kReplicaFloats = (int64_t) 1 << 23;
 
 int replicas_for_grid(int64_t G, unsigned flags) {
   if ((flags & (DRRT_DETERMINISTIC | DRRT_NO_REPLICAS)) || G < 4096) return 1;
+  const int forced = (int) ((flags >> 20) & 0xfu);  // DRRT_REPLICAS(n): the caller's choice, any grid size
+  if (forced > 1) return forced;
   const int64_t r = kReplicaFloats / G;
   return (int) (r < 1 ? 1 : r > kMaxReplicas ? kMaxReplicas : r);
 }
@@ -204,7 +206,7 @@ int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, i
     g_launches += launch_fixed_max(dx, dv, 3 * N, max_bits, s);
   }
   int R = scratch ? replicas_for_grid(G, flags) : 1;
-  if (R > 1) {
+  if (R > 1 && !((flags >> 20) & 0xfu)) {
     const int64_t by_rays = 8 * N / G;
     if (by_rays < R) R = by_rays < 1 ? 1 : (int) by_rays;
   }

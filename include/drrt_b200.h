@@ -88,6 +88,8 @@ enum {
   /* DRRT_NO_REPLICAS: one gradient grid for all CTAs even where the library would use private
    * copies (grids up to 2^23 / 2 voxels; see drrt_backtrace_scratch_bytes). */
   DRRT_NO_REPLICAS = 1u << 19,
+  /* bits 20-23  DRRT_REPLICAS(n), n in 2..15: force n gradient copies whatever the grid size
+   *             (a beam focused inside a LARGE grid; the scratch buffer grows to (n-1) grids). */
   DRRT_AUTO_INTERLEAVE = 1u << 18,
   /* Adjoint only: accumulate the gradient in 64-bit fixed point so the result is
    * bit-stable from run to run regardless of atomic ordering (and of the ray
@@ -101,6 +103,7 @@ enum {
 
 #define DRRT_AGG_RUN(n) ((unsigned) (n) << 8)
 #define DRRT_AGG_RUN_WARP (15u << 8)
+#define DRRT_REPLICAS(n) ((unsigned) (n) << 20)
 #define DRRT_INTERLEAVE(n) ((unsigned) (n) << 12)
 
 int drrt_abi_version(void);

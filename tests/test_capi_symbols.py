@@ -94,3 +94,6 @@ def test_scratch_bytes_contract(cuda_lib):
     assert f(32 ** 3, NOREP) == 0
     assert f(32 ** 3, DET) >= 8 * 32 ** 3 and f(32 ** 3, DET) == f(32 ** 3, DET | NOREP)
     assert f(256 ** 3, DET) >= 8 * 256 ** 3
+    REP = lambda n: n << 20                            # DRRT_REPLICAS(n): the caller's count, any grid size
+    assert f(256 ** 3, REP(3)) == 2 * 4 * 256 ** 3 and f(32 ** 3, REP(2)) == 4 * 32 ** 3
+    assert f(256 ** 3, REP(3) | NOREP) == 0 and f(256 ** 3, REP(3) | DET) == f(256 ** 3, DET)

@@ -221,10 +221,11 @@ def test_private_gradient_copies_only_change_the_summation_order(field, cuda_lib
     lib = _capi.load()
     G = rif.numel()
     assert lib.drrt_backtrace_scratch_bytes(G, 0) == 15 * 4 * G and lib.drrt_backtrace_scratch_bytes(G, NOREP) == 0
+    assert ops.make_flags(replicas=3) == 3 << 20 and ops.make_flags(replicas=False) == NOREP and ops.make_flags() == 0
     st = ops.new_stats("cuda")
     det = ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=DET, stats=st)
     steps = int(st[0])
-    for fl in (0, NOREP, REF, REF | NOREP, AGG, NOFC):
+    for fl in (0, NOREP, REF, REF | NOREP, AGG, NOFC, 3 << 20, 15 << 20):  # the last two: DRRT_REPLICAS(3), (15)
         st = ops.new_stats("cuda")
         gr = ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=fl, stats=st)
         assert int(st[0]) == steps
