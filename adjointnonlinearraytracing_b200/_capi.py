@@ -25,6 +25,7 @@ DRRT_SENSOR_FAR = 1 << 6
 DRRT_NO_FACE_CARRY = 1 << 7
 DRRT_AUTO_INTERLEAVE = 1 << 18
 DRRT_NO_REPLICAS = 1 << 19
+DRRT_FACE_CARRY = 1 << 24
 DRRT_AGG_RUN_WARP = 15 << 8
 
 

@@ -196,7 +196,11 @@ int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, i
   a.agg_policy = (int) ((flags >> 8) & 0xfu);  // experimental: DRRT_AGG_RUN(n), 0 = adaptive
   if (a.agg_policy == 15) a.agg_policy = 32;   // DRRT_AGG_RUN_WARP
   a.agg_t8 = 6; a.agg_twarp = 12;  // adaptive policy thresholds (profiles/r09_agg_policies.log)
-  a.face_carry = (flags & DRRT_NO_FACE_CARRY) ? 0 : 1;
+  // The face carry halves the atomics of a cell change and pays while cell changes are frequent; from
+  // ~6 steps per cell on its branchy flush costs more than the atomics it saves (Luneburg yaml shape:
+  // ds = h/4 7.2 vs 8.9 ms with / without, h/8 12.6 vs 11.1, h/32 39.3 vs 37.4;
+  // profiles/r09_facecarry_vs_step.log), so it is chosen from h/ds unless a flag decides.
+  a.face_carry = (flags & DRRT_NO_FACE_CARRY) ? 0 : (flags & DRRT_FACE_CARRY) ? 1 : (h < 6.0f * ds ? 1 : 0);
   unsigned long long *fixed = nullptr;
   unsigned *max_bits = nullptr;
   if (det) {

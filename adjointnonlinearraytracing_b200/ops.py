@@ -30,11 +30,12 @@ __all__ = [
 
 def make_flags(reference_arith: bool = False, deterministic: bool = False,
                accumulate: bool = False, fast_arith: bool = False,
-               warp_aggregation: bool = False, interleave=None, face_carry: bool = True,
+               warp_aggregation: bool = False, interleave=None, face_carry=None,
                replicas=True) -> int:
     """Flag word of the C ABI (include/drrt_b200.h).  Default arithmetic = exact trajectory;
     `interleave`: None = the library default (off with the face carry), 0/False = off,
-    "auto" = measured on the device, 2^k = forced; `replicas`: True = private gradient copies on small
+    "auto" = measured on the device, 2^k = forced; `face_carry`: None = chosen from h/ds, True / False = forced;
+    `replicas`: True = private gradient copies on small
     grids (the library's choice), False = one grid, n in 2..15 = that many copies on any grid."""
     if reference_arith and fast_arith:
         raise ValueError("reference_arith and fast_arith are mutually exclusive")
@@ -43,7 +44,7 @@ def make_flags(reference_arith: bool = False, deterministic: bool = False,
             | (DRRT_ACCUMULATE if accumulate else 0)
             | (DRRT_FAST_ARITH if fast_arith else 0)
             | (DRRT_WARP_AGGREGATION if warp_aggregation else 0)
-            | (0 if face_carry else _capi.DRRT_NO_FACE_CARRY)
+            | (0 if face_carry is None else _capi.DRRT_FACE_CARRY if face_carry else _capi.DRRT_NO_FACE_CARRY)
             | (0 if replicas is True else _capi.DRRT_NO_REPLICAS if not replicas else _capi.DRRT_REPLICAS(replicas))
             | (0 if interleave is None else _capi.DRRT_AUTO_INTERLEAVE if interleave == "auto"
                else DRRT_NO_INTERLEAVE if not interleave else DRRT_INTERLEAVE(interleave)))

@@ -85,6 +85,9 @@ enum {
    * also restores the device-measured interleave as the default, i.e. the r03/r04 kernel).
    * DRRT_AUTO_INTERLEAVE: measure the interleave on the device even with the face carry. */
   DRRT_NO_FACE_CARRY = 1u << 7,
+  /* DRRT_FACE_CARRY: use the face carry whatever the step size (the default uses it when a ray takes
+   * fewer than 6 steps per cell, ds > h/6, where it pays). */
+  DRRT_FACE_CARRY = 1u << 24,
   /* DRRT_NO_REPLICAS: one gradient grid for all CTAs even where the library would use private
    * copies (grids up to 2^23 / 2 voxels; see drrt_backtrace_scratch_bytes). */
   DRRT_NO_REPLICAS = 1u << 19,

@@ -29,6 +29,7 @@ FAST = 8  # DRRT_FAST_ARITH
 AGG = 16  # DRRT_WARP_AGGREGATION
 NOIL = 32  # DRRT_NO_INTERLEAVE
 NOFC = 1 << 7  # DRRT_NO_FACE_CARRY
+FC = 1 << 24  # DRRT_FACE_CARRY (forced; the default decides from h/ds)
 
 
 @pytest.fixture(scope="module")
@@ -188,7 +189,8 @@ def test_seeded_vs_restatement(ng, s, field, ops, oracle_mod):
 @pytest.mark.parametrize("step_res", [8, 32])
 def test_fine_steps_many_per_cell(step_res, ops, oracle_mod):
     """ds = h/8 and h/32 (the reference's Luneburg yaml runs step_res 32): the register cell cache and
-    the face-carry flush hold a cell for dozens of steps; path and gradient still match the restatement."""
+    the face-carry flush (forced here: from 6 steps per cell on the default flushes all eight corners) hold a
+    cell for dozens of steps; path and gradient still match the restatement."""
     from adjointnonlinearraytracing_b200 import scenes as sc
     ng, s = 17, 40
     rif = sc.field_luneburg(ng)
@@ -200,7 +202,7 @@ def test_fine_steps_many_per_cell(step_res, ops, oracle_mod):
     xd, vd = ops.trace(T(rif), T(pos), T(vel), h, ds, stats=st)
     assert np.array_equal(N(xd), xp) and np.array_equal(N(vd), vp) and int(st[0]) == steps_f
     gp = oracle_mod.port.backtrace(rif, xp, vp, dx, dv, h, ds); steps_b = oracle_mod.port.last_steps
-    for fl in (REF, 0, NOFC, NOIL, AGG, DET):
+    for fl in (REF, 0, NOFC, FC, FC | AGG, NOIL, AGG, DET, DET | FC):
         st = ops.new_stats("cuda")
         gd = ops.backtrace(T(rif), T(xp), T(vp), T(dx), T(dv), h, ds, flags=fl, stats=st)
         assert int(st[0]) == steps_b

@@ -1,7 +1,7 @@
 """Dev script (GPU box): one forward + N adjoint launches of a named workload with given flags --
 the thing to put under ncu.
 
-    python tools/gpu_one.py <caustic|cone|fuel|focal|luneburg> <flags> [reps]
+    python tools/gpu_one.py <caustic|cone|fuel|focal|luneburg|lunyaml> <flags,flags,...> [reps] [step_res]
 """
 import os
 import sys
@@ -43,13 +43,14 @@ if __name__ == "__main__":
     flag_list = [int(f, 0) for f in sys.argv[2].split(",")]
     reps = int(sys.argv[3]) if len(sys.argv) > 3 else 1
     ng, pos, vel = CASES[name]()
-    rif = T(FIELD.get(name, sc.field_bump)(ng)); h = float(sc.grid_spacing(ng)); ds = h / STEP_RES.get(name, 2)
+    step_res = int(sys.argv[4]) if len(sys.argv) > 4 else STEP_RES.get(name, 2)
+    rif = T(FIELD.get(name, sc.field_bump)(ng)); h = float(sc.grid_spacing(ng)); ds = h / step_res
     pos, vel = T(pos), T(vel)
     one = torch.ones_like(pos)
     st = ops.new_stats(dev)
     a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
     a.record(); xt, vt = ops.trace(rif, pos, vel, h, ds, stats=st); b.record(); torch.cuda.synchronize()
-    print(f"{name} fwd {a.elapsed_time(b):.3f} ms, {int(st[0])} ray-steps, {pos.shape[0]} rays", flush=True)
+    print(f"{name} ds = h/{step_res} fwd {a.elapsed_time(b):.3f} ms, {int(st[0])} ray-steps, {pos.shape[0]} rays", flush=True)
     g0 = None
     for fl in flag_list:
         for _ in range(reps):
