@@ -67,8 +67,8 @@ enum {
    * few rays per 10^4 take the other branch at a cell face. */
   DRRT_REFERENCE_ARITH = 1u << 0,
   DRRT_FAST_ARITH = 1u << 3,
-  /* Adjoint only, A/B switches for profiling (defaults: face-carry flush, no interleave,
-   * no warp aggregation).
+  /* Adjoint only, A/B switches for profiling (defaults: face-carry flush when ds > h/6, private
+   * gradient copies on small grids, no interleave, no warp aggregation).
    * DRRT_NO_INTERLEAVE: ray i on thread i instead of the strided assignment that puts
    * the lanes of a warp into different cells.
    * DRRT_WARP_AGGREGATION: pre-sum lanes that flush the same cell with a segmented
@@ -90,10 +90,10 @@ enum {
   DRRT_FACE_CARRY = 1u << 24,
   /* DRRT_NO_REPLICAS: one gradient grid for all CTAs even where the library would use private
    * copies (grids up to 2^23 / 2 voxels; see drrt_backtrace_scratch_bytes). */
+  DRRT_AUTO_INTERLEAVE = 1u << 18,
   DRRT_NO_REPLICAS = 1u << 19,
   /* bits 20-23  DRRT_REPLICAS(n), n in 2..15: force n gradient copies whatever the grid size
    *             (a beam focused inside a LARGE grid; the scratch buffer grows to (n-1) grids). */
-  DRRT_AUTO_INTERLEAVE = 1u << 18,
   /* Adjoint only: accumulate the gradient in 64-bit fixed point so the result is
    * bit-stable from run to run regardless of atomic ordering (and of the ray
    * order / interleave). */
