@@ -213,6 +213,21 @@ __global__ void __launch_bounds__(kTraceThreads, KIND == K_PLAIN ? kTraceMinBloc
       a.tail_iters[r] = i;
       atomicMax(a.tail_max_iters, i);
     }
+    if (KIND == K_SDF) {
+      // A ray that left the GRID while still inside the sdf (escaped, not crossed, inside) keeps being
+      // integrated by the reference -- clamped samples beyond the box -- for as long as the batch's loop
+      // runs, and its crossing is captured then (src/tracer.cpp:279-303): state for trace_sdf_tail_kernel.
+      const bool more = esc && !crossed && inside;
+      a.tail_iters[r] = more ? i : 0x7fffffff;
+      if (more) {
+        st3(a.tail_x, r, a.N, DRRT_LAYOUT_SOA, x);
+        st3(a.tail_v, r, a.N, DRRT_LAYOUT_SOA, v);
+      }
+    }
+  }
+  if (KIND == K_SDF) {  // the batch's loop runs until its last ray has escaped (or to the cap)
+    const int wmax = __reduce_max_sync(0xffffffffu, valid ? steps : 0);
+    if ((threadIdx.x & 31) == 0 && wmax) atomicMax(a.tail_max_iters, wmax);
   }
   if (a.stats) {
     const int64_t wsteps = warp_sum_i64((int64_t) steps);
@@ -252,6 +267,43 @@ __global__ void __launch_bounds__(kTraceThreads) trace_target_tail_kernel(TraceA
     st3(a.xt, r, a.N, a.layout, bx);
     st3(a.vt, r, a.N, a.layout, v);
     a.dist2[r] = best;
+  }
+}
+
+// trace_sdf couples rays the same way in one corner case: a ray that leaves the grid while the sdf
+// still says "inside" (an object reaching the boundary of the volume) has escaped but not crossed; the
+// reference's loop goes on until every ray of the batch has escaped, and while it does this ray keeps
+// stepping with `inside` set -- refractive index and sdf sampled at clamped positions beyond the box --
+// and the first sdf >= 0 sample is captured as its exit state (src/tracer.cpp:279-303).  This kernel
+// replays those iterations up to the batch-wide count found by trace_kernel<K_SDF>.
+template <int AR>
+__global__ void __launch_bounds__(kTraceThreads) trace_sdf_tail_kernel(TraceArgs a) {
+  constexpr bool REF = AR != A_FAST;
+  const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= a.N) return;
+  const int total = *a.tail_max_iters;
+  int i = a.tail_iters[r];
+  if (i >= total) return;
+  const GridP g = a.grid;
+  GridP sg = g;
+  sg.data = a.sdf;
+  const float ds = a.ds;
+  f3 x = ld3(a.tail_x, r, a.N, DRRT_LAYOUT_SOA), v = ld3(a.tail_v, r, a.N, DRRT_LAYOUT_SOA);
+  CellCache<AR> cc, sc;
+  cc.reset(); sc.reset();
+  for (; i < total; ++i) {
+    CellIdx c = cell_of(g, x);
+    if (cc.differs(c)) cc.refill(g, c);
+    float n; f3 nx;
+    cc.eval(g, c, n, nx, nullptr);
+    float dsn = REF ? mul_(ds, n) : ds * n;
+    v.x = fmaf(dsn, nx.x, v.x); v.y = fmaf(dsn, nx.y, v.y); v.z = fmaf(dsn, nx.z, v.z);
+    x.x = fmaf(ds, v.x, x.x); x.y = fmaf(ds, v.y, x.y); x.z = fmaf(ds, v.z, x.z);
+    if (!(eval_value<AR>(sg, sc, x) < 0.f)) {  // crossed: captured, and never inside again
+      st3(a.xt, r, a.N, a.layout, x);
+      st3(a.vt, r, a.N, a.layout, v);
+      return;
+    }
   }
 }
 
@@ -631,7 +683,11 @@ int launch_trace(int kind, int arith, const TraceArgs &a, cudaStream_t s) {
   switch (kind) {
     case K_PLAIN: launch_trace_kind<K_PLAIN>(arith, a, s); return 1;
     case K_PLANE: launch_trace_kind<K_PLANE>(arith, a, s); return 1;
-    case K_SDF: launch_trace_kind<K_SDF>(arith, a, s); return 1;
+    case K_SDF:
+      launch_trace_kind<K_SDF>(arith, a, s);
+      if (arith == A_FAST) trace_sdf_tail_kernel<A_FAST><<<blocks_for(a.N, kTraceThreads), kTraceThreads, 0, s>>>(a);
+      else trace_sdf_tail_kernel<A_REF><<<blocks_for(a.N, kTraceThreads), kTraceThreads, 0, s>>>(a);
+      return 2;
     case K_TARGET:
       launch_trace_kind<K_TARGET>(arith, a, s);
       trace_target_tail_kernel<<<blocks_for(a.N, kTraceThreads), kTraceThreads, 0, s>>>(a);
