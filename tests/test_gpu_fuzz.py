@@ -85,3 +85,48 @@ def test_random_shapes_match_the_restatement(seed, cuda_lib, oracle_mod):
     g2, dp2, dv2 = ops.backtrace_rays(T(rif), T(xp), T(vp), T(dx), T(dv), h, ds, pos0=T(pos), res=res)
     assert rel_l2(N(g2), gr) <= 2e-5
     assert rel_l2(N(dp2), dpos) <= 1e-4 and rel_l2(N(dv2), dvel) <= 1e-4
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_random_target_batches_match_the_restatement(seed, cuda_lib, oracle_mod):
+    """trace_target is batch-coupled (every ray is tested for a new closest approach until the LAST ray has
+    escaped): random batches, targets inside and beyond the volume."""
+    from adjointnonlinearraytracing_b200 import ops
+    res, h, ds, rif, pos, vel, rng = draw(100 + seed)
+    n = len(pos)
+    ext = (np.array(res) - 1) * float(h)
+    target = (rng.uniform(-0.3, 1.3, (n, 3)) * ext).astype(np.float32)
+    xp, vp, dp = oracle_mod.port.trace_target(rif, pos, vel, target, h, ds, res=res)
+    for fl in (0, REF):
+        xt, vt, d2 = ops.trace_target(T(rif), T(pos), T(vel), T(target), h, ds, res=res, flags=fl)
+        assert np.array_equal(N(xt), xp) and np.array_equal(N(vt), vp) and np.array_equal(N(d2), dp), (seed, fl)
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_random_cables_match_the_restatement(seed, cuda_lib, oracle_mod):
+    """Cylinder variant: random profile resolution, radius, length, step and rays entering the face y = 0
+    (some grazing the wall, some starting outside the radius)."""
+    from adjointnonlinearraytracing_b200 import ops
+    rng = np.random.default_rng(2000 + seed)
+    res = int(rng.integers(6, 220))
+    radius = float(rng.uniform(0.3, 2.0)); length = float(rng.uniform(0.5, 4.0))
+    ds = np.float32(radius / res / [0.5, 1, 2, 3][seed % 4])
+    r = np.linspace(0, 1, res)
+    prof = (rng.uniform(1.2, 1.6) * (1 - rng.uniform(0.01, 0.1) * r * r) + rng.uniform(0, 0.003) * rng.uniform(0, 1, res)).astype(np.float32)
+    n = int(rng.integers(100, 1500))
+    rr = rng.uniform(0, 1.05, n) ** 0.5 * radius
+    th = rng.uniform(0, 2 * np.pi, n)
+    pos = np.stack([radius + rr * np.cos(th), rng.uniform(0, 2e-3, n), radius + rr * np.sin(th)], axis=1).astype(np.float32)
+    vel = np.array([0, 1, 0]) + rng.uniform(0.01, 0.4) * rng.standard_normal((n, 3))
+    vel = (vel / np.linalg.norm(vel, axis=1, keepdims=True)).astype(np.float32)
+    target = np.tile(np.array([radius, length, radius], np.float32), (n, 1)) + 0.1 * rng.standard_normal((n, 3)).astype(np.float32)
+    port = oracle_mod.port
+    xp, vp, dp = port.trace_cable(prof, radius, length, pos, vel, target, ds)
+    st = ops.new_stats("cuda")
+    xt, vt, d2 = ops.trace_cable(T(prof), radius, length, T(pos), T(vel), T(target), ds, stats=st)
+    assert np.array_equal(N(xt), xp) and np.array_equal(N(vt), vp) and np.array_equal(N(d2), dp), seed
+    dx = rng.standard_normal((n, 3)).astype(np.float32); dv = rng.standard_normal((n, 3)).astype(np.float32)
+    gp = port.backtrace_cable(prof, radius, length, xp, vp, dx, dv, ds)
+    for fl in (0, DET, REF, REF | DET):
+        gg = ops.backtrace_cable(T(prof), radius, length, T(xp), T(vp), T(dx), T(dv), ds, flags=fl)
+        assert rel_l2(N(gg), gp) <= 1e-4, (seed, fl, rel_l2(N(gg), gp))
