@@ -130,3 +130,59 @@ def test_random_cables_match_the_restatement(seed, cuda_lib, oracle_mod):
     for fl in (0, DET, REF, REF | DET):
         gg = ops.backtrace_cable(T(prof), radius, length, T(xp), T(vp), T(dx), T(dv), ds, flags=fl)
         assert rel_l2(N(gg), gp) <= 1e-4, (seed, fl, rel_l2(N(gg), gp))
+
+
+def _grad_close(a, b, tol=2e-3, frac=0.985):
+    scale = max(np.abs(b).max(), 1e-30)
+    err = np.abs(a - b).max(axis=1) / scale
+    assert np.mean(err <= tol) >= frac, (float(np.mean(err <= tol)), float(err.max()))
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_random_sensor_planes_match_the_restatement(seed, cuda_lib):
+    """Sensor epilogue with oblique planes, explicit and default tangents, odd and even resolutions, per-ray
+    energies, rays that miss the sensor; near field, far field and the two texture look-ups."""
+    from oracle import sensor_oracle as so
+    from adjointnonlinearraytracing_b200 import sensor
+    rng = np.random.default_rng(3000 + seed)
+    n = int(rng.integers(2000, 20000))
+    nn = rng.standard_normal(3); nn[2] = abs(nn[2]) + 0.7; nn /= np.linalg.norm(nn)
+    nn = nn[None]
+    tg = None
+    if seed % 2:
+        t = rng.standard_normal(3); t -= (t @ nn[0]) * nn[0]; tg = (t / np.linalg.norm(t))[None]
+    p = np.array([[0.5, 0.5, 1.0 + rng.uniform(0, 0.5)]])
+    res = int(rng.integers(5, 70)); span = float(rng.uniform(0.6, 2.0))
+    x = np.stack([rng.uniform(-0.1, 1.1, n), rng.uniform(-0.1, 1.1, n), rng.uniform(0.6, 1.0, n)], axis=1)
+    v = nn[0] + rng.uniform(0.02, 0.3) * rng.standard_normal((n, 3))
+    e = rng.uniform(0.2, 2.0, n) if seed % 3 == 0 else float(rng.uniform(0.5, 2.0))
+    dimg = rng.standard_normal((res, res))
+    for mode in ("near", "far"):
+        sp = span if mode == "near" else float(rng.uniform(40, 150))
+        img64, dx64, dv64 = so.run(mode, x, v, e, p, nn, tg, res, sp, dimg)
+        xg = T(x.astype(np.float32)).requires_grad_(True); vg = T(v.astype(np.float32)).requires_grad_(True)
+        eg = T(np.asarray(e, np.float32)) if np.ndim(e) else e
+        plane = (T(p.astype(np.float32)), T(nn.astype(np.float32)))
+        tt = None if tg is None else T(tg.astype(np.float32))
+        if mode == "near":
+            img = sensor.generate_sensor((xg, vg), eg, plane, res, sp, tt)
+        else:
+            img = sensor.generate_inf_sensor((xg, vg), eg, plane, res, angle_span=sp, tangent=tt)
+        (img * T(dimg.astype(np.float32))).sum().backward()
+        assert np.abs(N(img) - img64).max() <= 5e-5 * max(np.abs(img64).max(), 1e-30), (seed, mode)
+        _grad_close(N(vg.grad), dv64)
+        if mode == "near":
+            _grad_close(N(xg.grad), dx64)
+        # texture look-ups at the same coordinates
+        tex = rng.uniform(-1, 1, (res, res))
+        df = rng.standard_normal(n)
+        f64, gx64, gv64 = so.run_gather(mode, x, v, tex, p, nn, tg, sp, df)
+        xg = T(x.astype(np.float32)).requires_grad_(True); vg = T(v.astype(np.float32)).requires_grad_(True)
+        fn = sensor.get_sdf_vals_near if mode == "near" else sensor.get_sdf_vals_far
+        f = fn((xg, vg), T(tex.astype(np.float32)), plane, sp, tt)
+        (f * T(df.astype(np.float32))).sum().backward()
+        err = np.abs(N(f) - f64)
+        assert np.mean(err <= 2e-4) >= 0.99, (seed, mode, float(err.max()))
+        _grad_close(N(vg.grad), gv64)
+        if mode == "near":
+            _grad_close(N(xg.grad), gx64)
