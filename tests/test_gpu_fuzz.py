@@ -186,3 +186,40 @@ def test_random_sensor_planes_match_the_restatement(seed, cuda_lib):
         _grad_close(N(vg.grad), gv64)
         if mode == "near":
             _grad_close(N(xg.grad), gx64)
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_random_plane_sources_match_the_restatement(seed, cuda_lib):
+    """Ray generation from caller uniforms: random view counts, non-square pixel grids, samples per pixel,
+    widths, sensor distances, circle filter, independent jitter, x-axis rotations; the six cube faces with
+    the fused rigid rotation."""
+    from oracle import source_oracle as so
+    from adjointnonlinearraytracing_b200 import source
+    rng = np.random.default_rng(4000 + seed)
+    nviews = int(rng.integers(1, 8)); P = (int(rng.integers(3, 40)), int(rng.integers(3, 40))); spp = int(rng.integers(1, 6))
+    width = float(rng.uniform(0.5, 3.0)); sd = float(rng.uniform(0.0, 1.5)); span = float(rng.choice([90, 180, 270, 360]))
+    circle = bool(seed % 2); xaxis = bool((seed // 2) % 2); indep = bool((seed // 4) % 2)
+    u = rng.uniform(0, 1, (nviews, 2 * spp, P[0], P[1])).astype(np.float32)
+    tol = 3e-6 * max(1.0, width + sd)
+
+    def close(t, ref):
+        a = N(t).astype(np.float64)
+        assert a.shape == ref.shape, (a.shape, ref.shape)
+        assert np.abs(a - ref).max() <= tol, float(np.abs(a - ref).max())
+
+    x64, v64, pl64, nr64 = so.multi_view(so.sphere_views(nviews, span, xaxis), u.astype(np.float64), P, spp, width, circle, sd,
+                                         indep)
+    (x, v, pl), nr = source.rand_rays_in_sphere(nviews, P, spp, width, angle_span=span, circle=circle, xaxis=xaxis,
+                                                sensor_dist=sd, indep=indep, offset=T(u))
+    assert nr == nr64
+    close(x, x64); close(v, v64); close(pl, pl64)
+    # cube faces + rigid rotation about the centre
+    q = rng.standard_normal((3, 3)); R, _ = np.linalg.qr(q)
+    if np.linalg.det(R) < 0:
+        R[:, 0] = -R[:, 0]
+    u6 = rng.uniform(0, 1, (6, 2 * spp, P[0], P[1])).astype(np.float32)
+    x64, v64, pl64, nr64 = so.multi_view(so.cube_views(), u6.astype(np.float64), P, spp, width, circle, 0.0, False)
+    x64, v64, pl64 = so.random_rotate_ic(x64, v64, pl64, width, R)
+    (x, v, pl), nr = source.rand_rays_cube(P, spp, width, circle=circle, offset=T(u6), rotmat=R)
+    assert nr == nr64
+    close(x, x64); close(v, v64); close(pl, pl64)
