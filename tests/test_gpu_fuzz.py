@@ -223,3 +223,38 @@ def test_random_plane_sources_match_the_restatement(seed, cuda_lib):
     (x, v, pl), nr = source.rand_rays_cube(P, spp, width, circle=circle, offset=T(u6), rotmat=R)
     assert nr == nr64
     close(x, x64); close(v, v64); close(pl, pl64)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_random_adam_and_upres_shapes_match_torch(seed, cuda_lib):
+    """Fused optimiser step on random (non-cubic, odd and multiple-of-4 innermost) shapes against
+    torch.optim.Adam + the reference's boundary mask and clamp; up-res against the float64 restatement."""
+    from oracle import optim_oracle as oo
+    from adjointnonlinearraytracing_b200 import ops
+    rng = np.random.default_rng(5000 + seed)
+    shape = tuple(int(s) for s in rng.integers(3, 41, 3))
+    if seed % 2 == 0:
+        shape = shape[:2] + (4 * max(1, shape[2] // 4),)  # the float4 kernel
+    lr = float(rng.choice([1e-3, 1e-2, 5e-2])); betas = (float(rng.uniform(0.8, 0.95)), float(rng.uniform(0.99, 0.9999)))
+    n0 = (1 + 0.2 * rng.uniform(0, 1, shape)).astype(np.float32)
+    p = torch.from_numpy(n0.copy()).cuda().requires_grad_(True)
+    opt = torch.optim.Adam([p], lr=lr, betas=betas)
+    n = torch.from_numpy(n0.copy()).cuda(); m = torch.zeros_like(n); v = torch.zeros_like(n)
+    mask = torch.ones(shape, dtype=torch.bool, device="cuda"); mask[1:-1, 1:-1, 1:-1] = False
+    for step in range(1, 6):
+        g = torch.from_numpy(rng.standard_normal(shape).astype(np.float32) * 10.0 ** rng.uniform(-4, 1)).cuda()
+        p.grad = g.clone(); p.grad[mask] = 0
+        opt.step()
+        with torch.no_grad():
+            p.clamp_(min=1)
+        ops.adam_step_(n, g, m, v, step, lr, betas)
+        assert float((n - p.detach()).abs().max()) <= 3e-6, (seed, step)
+    assert torch.equal(n[mask], torch.from_numpy(n0).cuda()[mask])
+    st = opt.state[p]
+    assert float((m - st["exp_avg"]).abs().max()) <= 1e-6 * max(1.0, float(st["exp_avg"].abs().max()))
+    # up-res of a cubic grid (the reference only up-samples cubes)
+    s0 = int(rng.integers(3, 24)); s1 = int(rng.integers(s0, 48))
+    a = rng.uniform(1, 2, (s0, s0, s0)).astype(np.float32)
+    up = ops.upres_volume(torch.from_numpy(a).cuda(), [s1] * 3)
+    ref = oo.upres_volume(a, [s1] * 3)
+    assert up.shape == (s1, s1, s1) and np.abs(N(up) - np.asarray(ref)).max() <= 2e-6
