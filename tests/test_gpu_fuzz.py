@@ -60,6 +60,13 @@ def test_random_shapes_match_the_restatement(seed, cuda_lib, oracle_mod):
         st = ops.new_stats("cuda")
         xt, vt = ops.trace(T(rif), T(pos), T(vel), h, ds, res=res, flags=fl, stats=st)
         assert np.array_equal(N(xt), xp) and np.array_equal(N(vt), vp) and int(st[0]) == sf, (seed, fl)
+    if seed % 3 == 0:  # SoA layout and the host-buffer entry points (TracerS)
+        from adjointnonlinearraytracing_b200 import drrt
+        xs_, vs_ = ops.trace(T(rif), T(pos.T.copy()), T(vel.T.copy()), h, ds, res=res, layout="soa")
+        assert np.array_equal(N(xs_).T, xp) and np.array_equal(N(vs_).T, vp)
+        ts = drrt.TracerS()
+        xh, vh = ts.trace(rif, res, pos, vel, h, ds)
+        assert np.array_equal(xh.numpy(), xp) and np.array_equal(vh.numpy(), vp) and ts.last_stats[0] == sf
     # plane and sdf variants
     po = (pos + rng.uniform(0.2, 2.0, (n, 1)).astype(np.float32) * vel).astype(np.float32)
     xq, vq, mq = port.trace_pln(rif, pos, vel, po, vel, h, ds, res=res)
@@ -77,6 +84,12 @@ def test_random_shapes_match_the_restatement(seed, cuda_lib, oracle_mod):
         gg = ops.backtrace(T(rif), T(xp), T(vp), T(dx), T(dv), h, ds, res=res, flags=fl, stats=st)
         assert int(st[0]) == sb, (seed, fl)
         assert rel_l2(N(gg), gp) <= 2e-5, (seed, fl, rel_l2(N(gg), gp))
+    if seed % 3 == 0:
+        gsoa = ops.backtrace(T(rif), T(xp.T.copy()), T(vp.T.copy()), T(dx.T.copy()), T(dv.T.copy()), h, ds, res=res,
+                             layout="soa")
+        assert rel_l2(N(gsoa), gp) <= 2e-5
+        gh = ts.backtrace(rif, res, xp, vp, dx, dv, h, ds)
+        assert rel_l2(gh.numpy().reshape(-1), gp.reshape(-1)) <= 2e-5
     gs = port.backtrace_sdf(rif, sdf, xs, vs, dx, dv, h, ds, res=res)
     gsg = ops.backtrace_sdf(T(rif), T(sdf), T(xs), T(vs), T(dx), T(dv), h, ds, res=res)
     assert rel_l2(N(gsg), gs) <= 2e-5 or np.abs(gs).max() == 0
