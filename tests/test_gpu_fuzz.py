@@ -271,3 +271,41 @@ def test_random_adam_and_upres_shapes_match_torch(seed, cuda_lib):
     up = ops.upres_volume(torch.from_numpy(a).cuda(), [s1] * 3)
     ref = oo.upres_volume(a, [s1] * 3)
     assert up.shape == (s1, s1, s1) and np.abs(N(up) - np.asarray(ref)).max() <= 2e-6
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_random_point_cone_area_sources_match_the_restatement(seed, cuda_lib):
+    """The four non-plane source kinds, one random view each, from caller uniforms."""
+    from oracle import source_oracle as so
+    from adjointnonlinearraytracing_b200 import source
+    rng = np.random.default_rng(6000 + seed)
+    P = (int(rng.integers(3, 30)), int(rng.integers(3, 30))); spp = int(rng.integers(1, 5))
+    n = P[0] * P[1] * spp
+    width = float(rng.uniform(0.5, 2.5)); sd = float(rng.uniform(0.1, 1.5)); ang = float(rng.uniform(0, 360))
+    xaxis = bool(seed % 2); circle = bool((seed // 2) % 2); cone = float(rng.uniform(10, 170))
+    R = so.rotmat(np.float32(ang), xaxis)
+    tol = 4e-6 * max(1.0, width + sd)
+
+    def close(t, ref, scale=1.0):
+        a = N(t).astype(np.float64)
+        assert a.shape == ref.shape, (a.shape, ref.shape)
+        assert np.abs(a - ref).max() <= tol * scale, float(np.abs(a - ref).max())
+
+    u = rng.uniform(0, 1, (2 * spp, P[0], P[1])).astype(np.float32)
+    x64, v64, pl64, keep = so.point_source3_rand(R, u.astype(np.float64), P, spp, width, circle, sd)
+    x, v, pl = source.point_source3_rand(ang, P, spp, width, circle=circle, xaxis=xaxis, sensor_dist=sd, offset=T(u))
+    close(x, x64); close(v, v64); close(pl, pl64)
+    u = rng.uniform(0, 1, (2, n)).astype(np.float32)
+    x64, v64, pl64, _ = so.cone_source3_rand(R, u.astype(np.float64), P, spp, width, sd, cone)
+    x, v, pl = source.cone_source3_rand(ang, P, spp, width, xaxis=xaxis, sensor_dist=sd, cone_angle=cone, offset=T(u))
+    close(x, x64); close(v, v64, 2.0); close(pl, pl64)
+    u = rng.uniform(0, 1, (4, n)).astype(np.float32)
+    cone2 = float(rng.uniform(10, 150))  # tpv = sensor_dist / v.y: keep v.y away from 0
+    x64, v64, pl64, tpv64 = so.area_source3_cone(R, u.astype(np.float64), P, spp, width, sd, cone2)
+    (x, v, pl), tpv = source.area_source3_cone(ang, P, spp, width, xaxis=xaxis, sensor_dist=sd, cone_angle=cone2, offset=T(u))
+    close(x, x64); close(v, v64, 2.0); close(pl, pl64)
+    assert np.abs(N(tpv) - tpv64).max() <= 1e-5 * np.abs(tpv64).max()
+    x64, v64, pl64, xt64, tpv64 = so.area_source3_rand_bias(R, u.astype(np.float64), P, spp, width, sd)
+    (x, v, pl), xt, tpv = source.area_source3_rand_bias(ang, P, spp, width, xaxis=xaxis, sensor_dist=sd, offset=T(u))
+    close(x, x64, 2.0); close(v, v64); close(pl, pl64); close(xt, xt64)
+    assert np.abs(N(tpv) - tpv64).max() <= 1e-5 * np.abs(tpv64).max()
