@@ -135,8 +135,8 @@ int trace_common(int kind, const float *rif, const float *sdf, int W, int H, int
   a.max_steps = cap_grid(kind == 3 ? 2.0f : 4.0f, h, W, H, D, ds);
   a.xt = xt; a.vt = vt; a.not_escaped = not_escaped; a.dist2 = dist2; a.stats = stats;
   void *tail = nullptr;
-  if (kind == 2 || kind == 3) {
-    // SoA scratch for the batch-coupled tails (trace_target, trace_sdf): x, v (3N floats each), iters (N), max (1)
+  if (kind >= 1) {
+    // SoA scratch for the batch-coupled tails (trace_plane, trace_target, trace_sdf): x, v (3N floats each), iters (N), max (1)
     size_t bytes = sizeof(float) * 6 * (size_t) N + sizeof(int) * ((size_t) N + 4);
     CU_TRY(cudaMallocAsync(&tail, bytes, s));
     a.tail_x = (float *) tail;

@@ -213,6 +213,20 @@ __global__ void __launch_bounds__(kTraceThreads, KIND == K_PLAIN ? kTraceMinBloc
       a.tail_iters[r] = i;
       atomicMax(a.tail_max_iters, i);
     }
+    if (KIND == K_PLANE) {
+      // A ray stopped by its plane INSIDE the grid flies on straight (masked gathers) while the batch's loop
+      // runs; if it moves against the plane normal it comes back to the near side, is "inside" again, bends
+      // again and its next crossing overwrites the captured state (src/tracer.cpp:144-152 has no
+      // `!escaped` on `cross`): state for trace_plane_tail_kernel.  With v.d > 0 the plane distance only grows.
+      const float vd = fmaf(v.z, aux1.z, fmaf(v.y, aux1.y, v.x * aux1.x));
+      const float tiny = 1e-5f * sqrtf((v.x * v.x + v.y * v.y + v.z * v.z) * (aux1.x * aux1.x + aux1.y * aux1.y + aux1.z * aux1.z));
+      const bool more = esc && inbounds(g, x) && !(vd > tiny);
+      a.tail_iters[r] = more ? i : 0x7fffffff;
+      if (more) {
+        st3(a.tail_x, r, a.N, DRRT_LAYOUT_SOA, x);
+        st3(a.tail_v, r, a.N, DRRT_LAYOUT_SOA, v);
+      }
+    }
     if (KIND == K_SDF) {
       // A ray that left the GRID while still inside the sdf (escaped, not crossed, inside) keeps being
       // integrated by the reference -- clamped samples beyond the box -- for as long as the batch's loop
@@ -225,7 +239,7 @@ __global__ void __launch_bounds__(kTraceThreads, KIND == K_PLAIN ? kTraceMinBloc
       }
     }
   }
-  if (KIND == K_SDF) {  // the batch's loop runs until its last ray has escaped (or to the cap)
+  if (KIND == K_SDF || KIND == K_PLANE) {  // the batch's loop runs until its last ray has escaped (or to the cap)
     const int wmax = __reduce_max_sync(0xffffffffu, valid ? steps : 0);
     if ((threadIdx.x & 31) == 0 && wmax) atomicMax(a.tail_max_iters, wmax);
   }
@@ -304,6 +318,48 @@ __global__ void __launch_bounds__(kTraceThreads) trace_sdf_tail_kernel(TraceArgs
       st3(a.vt, r, a.N, a.layout, v);
       return;
     }
+  }
+}
+
+// trace_plane, same coupling (see trace_kernel<K_PLANE>): continue a ray that its plane stopped inside the
+// grid, for as long as the batch's loop runs -- straight while beyond the plane, bending again once it is
+// back on the near side -- and capture every later crossing like the reference does.
+template <int AR>
+__global__ void __launch_bounds__(kTraceThreads) trace_plane_tail_kernel(TraceArgs a) {
+  constexpr bool REF = AR != A_FAST;
+  const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= a.N) return;
+  const int total = *a.tail_max_iters;
+  int i = a.tail_iters[r];
+  if (i >= total) return;
+  const GridP g = a.grid;
+  const float ds = a.ds;
+  f3 x = ld3(a.tail_x, r, a.N, DRRT_LAYOUT_SOA), v = ld3(a.tail_v, r, a.N, DRRT_LAYOUT_SOA);
+  const f3 o = ld3(a.aux0, r, a.N, a.layout), d = ld3(a.aux1, r, a.N, a.layout);
+  CellCache<AR> cc;
+  cc.reset();
+  bool inside = false;  // it has just crossed
+  for (; i < total; ++i) {
+    if (inside) {
+      CellIdx c = cell_of(g, x);
+      if (cc.differs(c)) cc.refill(g, c);
+      float n; f3 nx;
+      cc.eval(g, c, n, nx, nullptr);
+      float dsn = REF ? mul_(ds, n) : ds * n;
+      v.x = fmaf(dsn, nx.x, v.x); v.y = fmaf(dsn, nx.y, v.y); v.z = fmaf(dsn, nx.z, v.z);
+    }
+    x.x = fmaf(ds, v.x, x.x); x.y = fmaf(ds, v.y, x.y); x.z = fmaf(ds, v.z, x.z);
+    const bool inb = inbounds(g, x);
+    float dd = mul_(sub_(x.x, o.x), d.x);
+    dd = fma_(sub_(x.y, o.y), d.y, dd);
+    dd = fma_(sub_(x.z, o.z), d.z, dd);
+    const bool cur_inside = inb & !(dd > 0.f);
+    if (inside & !cur_inside) {
+      st3(a.xt, r, a.N, a.layout, x);
+      st3(a.vt, r, a.N, a.layout, v);
+    }
+    inside = cur_inside;
+    if (!inb) return;  // out of the (convex) grid on a straight line: never inside again
   }
 }
 
@@ -682,7 +738,11 @@ int launch_trace(int kind, int arith, const TraceArgs &a, cudaStream_t s) {
   if (a.N <= 0) return 0;
   switch (kind) {
     case K_PLAIN: launch_trace_kind<K_PLAIN>(arith, a, s); return 1;
-    case K_PLANE: launch_trace_kind<K_PLANE>(arith, a, s); return 1;
+    case K_PLANE:
+      launch_trace_kind<K_PLANE>(arith, a, s);
+      if (arith == A_FAST) trace_plane_tail_kernel<A_FAST><<<blocks_for(a.N, kTraceThreads), kTraceThreads, 0, s>>>(a);
+      else trace_plane_tail_kernel<A_REF><<<blocks_for(a.N, kTraceThreads), kTraceThreads, 0, s>>>(a);
+      return 2;
     case K_SDF:
       launch_trace_kind<K_SDF>(arith, a, s);
       if (arith == A_FAST) trace_sdf_tail_kernel<A_FAST><<<blocks_for(a.N, kTraceThreads), kTraceThreads, 0, s>>>(a);

@@ -68,9 +68,11 @@ def test_random_shapes_match_the_restatement(seed, cuda_lib, oracle_mod):
         xh, vh = ts.trace(rif, res, pos, vel, h, ds)
         assert np.array_equal(xh.numpy(), xp) and np.array_equal(vh.numpy(), vp) and ts.last_stats[0] == sf
     # plane and sdf variants
-    po = (pos + rng.uniform(0.2, 2.0, (n, 1)).astype(np.float32) * vel).astype(np.float32)
-    xq, vq, mq = port.trace_pln(rif, pos, vel, po, vel, h, ds, res=res)
-    xg, vg, mg = ops.trace_pln(T(rif), T(pos), T(vel), T(po), T(vel), h, ds, res=res)
+    # planes behind the ray, inside the volume and beyond it; normals along the ray, tilted and facing it
+    po = (pos + (rng.uniform(-2, 40, (n, 1)) * float(h)).astype(np.float32) * vel).astype(np.float32)
+    pd = (vel + rng.uniform(0, 1.5) * rng.standard_normal((n, 3))).astype(np.float32)
+    xq, vq, mq = port.trace_pln(rif, pos, vel, po, pd, h, ds, res=res)
+    xg, vg, mg = ops.trace_pln(T(rif), T(pos), T(vel), T(po), T(pd), h, ds, res=res)
     assert np.array_equal(N(xg), xq) and np.array_equal(N(vg), vq) and np.array_equal(N(mg).astype(np.uint8), mq.astype(np.uint8))
     sdf = (rng.uniform(-1, 1, rif.shape) * 0.05 + 0.01).astype(np.float32)
     xs, vs = port.trace_sdf(rif, sdf, pos, vel, h, ds, res=res)
