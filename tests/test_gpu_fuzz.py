@@ -311,3 +311,47 @@ def test_random_point_cone_area_sources_match_the_restatement(seed, cuda_lib):
     (x, v, pl), xt, tpv = source.area_source3_rand_bias(ang, P, spp, width, xaxis=xaxis, sensor_dist=sd, offset=T(u))
     close(x, x64, 2.0); close(v, v64); close(pl, pl64); close(xt, xt64)
     assert np.abs(N(tpv) - tpv64).max() <= 1e-5 * np.abs(tpv64).max()
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_degenerate_rays_match_the_restatement(seed, cuda_lib, oracle_mod):
+    """Rays at rest, on the far faces and corners, sliding along faces and edges, axis-aligned on lattice
+    lines, and step sizes from far larger than the volume down to h/40 (loop caps computed in float)."""
+    from adjointnonlinearraytracing_b200 import ops
+    rng = np.random.default_rng(7000 + seed)
+    W, H, D = (int(v) for v in rng.integers(3, 20, 3))
+    h = np.float32([0.125, 0.1, 1.0 / 3, 0.25, 0.07, 1.0][seed])
+    ds = np.float32(h * [0.5, 40.0, 1.0, 0.025, 3.0, 0.5][seed])
+    ext = np.array([(W - 1), (H - 1), (D - 1)], np.float64) * float(h)
+    rif = (1.0 + 0.3 * rng.uniform(0, 1, W * H * D)).astype(np.float32)
+    P, V = [], []
+    for _ in range(40):
+        c = rng.integers(0, 2, 3) * ext                                    # corners
+        P.append(c); V.append(rng.standard_normal(3))
+        f = rng.uniform(0, 1, 3) * ext; k = rng.integers(0, 3); f[k] = ext[k] * rng.integers(0, 2)   # on a face
+        d = rng.standard_normal(3); d[k] = 0.0                              # sliding along it
+        P.append(f); V.append(d)
+        lat = np.floor(rng.uniform(0, 1, 3) * (np.array([W, H, D]) - 1)) * float(h)   # lattice point, axis-aligned
+        a = np.zeros(3); a[rng.integers(0, 3)] = rng.choice([-1.0, 1.0])
+        P.append(lat); V.append(a)
+        P.append(rng.uniform(0, 1, 3) * ext); V.append(np.zeros(3))        # at rest
+        P.append(rng.uniform(-0.5, 1.5, 3) * ext); V.append(rng.standard_normal(3) * rng.choice([1e-3, 1.0, 30.0]))
+    pos = np.array(P, np.float32); vel = np.array(V, np.float32)
+    res = (W, H, D)
+    port = oracle_mod.port
+    xp, vp = port.trace(rif, pos, vel, h, ds, res=res); sf = port.last_steps
+    st = ops.new_stats("cuda")
+    xt, vt = ops.trace(T(rif), T(pos), T(vel), h, ds, res=res, stats=st)
+    assert np.array_equal(N(xt), xp) and np.array_equal(N(vt), vp) and int(st[0]) == sf
+    n = len(pos)
+    dx = rng.standard_normal((n, 3)).astype(np.float32); dv = rng.standard_normal((n, 3)).astype(np.float32)
+    gp = port.backtrace(rif, xp, vp, dx, dv, h, ds, res=res); sb = port.last_steps
+    for fl in (0, REF, DET, FC, NOFC, AGG):
+        st = ops.new_stats("cuda")
+        gg = ops.backtrace(T(rif), T(xp), T(vp), T(dx), T(dv), h, ds, res=res, flags=fl, stats=st)
+        assert int(st[0]) == sb, (seed, fl, int(st[0]), sb)
+        assert rel_l2(N(gg), gp) <= 2e-5 or np.abs(gp).max() == 0, (seed, fl, rel_l2(N(gg), gp))
+    tgt = (rng.uniform(-0.2, 1.2, (n, 3)) * ext).astype(np.float32)
+    xq, vq, dq = port.trace_target(rif, pos, vel, tgt, h, ds, res=res)
+    xg, vg, dg = ops.trace_target(T(rif), T(pos), T(vel), T(tgt), h, ds, res=res)
+    assert np.array_equal(N(xg), xq) and np.array_equal(N(vg), vq) and np.array_equal(N(dg), dq)
