@@ -27,7 +27,7 @@ NOREP = 1 << 19
 if len(sys.argv) > 2 and sys.argv[2] == "replicas":
     FLAGS = [("one grid", NOREP), ("replicas", 0), ("replicas + agg warp", AGG | (15 << 8))]
 elif len(sys.argv) > 2 and sys.argv[2] == "forced":
-    FLAGS = [("one grid", NOREP)] + [(f"{n} copies", n << 20) for n in (2, 3, 4, 8)]
+    FLAGS = [("one grid", NOREP), ("default", 0)] + [(f"{n} copies", n << 20) for n in (2, 4, 8, 15)]
 else:
     FLAGS = [(n, f | NOREP) for n, f in FLAGS]
 CASES = [("lens 32^3, 256^2", 32, 2, sc.field_luneburg, lambda: sc.rays_collimated(256)),
@@ -37,6 +37,12 @@ CASES = [("lens 32^3, 256^2", 32, 2, sc.field_luneburg, lambda: sc.rays_collimat
          ("lens 64^3, 512^2", 64, 2, sc.field_luneburg, lambda: sc.rays_collimated(512)),
          ("bump 64^3, 512^2", 64, 2, sc.field_bump, lambda: sc.rays_collimated(512)),
          ("fuel 65^3, 32 views", 65, 2, sc.field_bump, lambda: multiview_rays(32, 64, 16))]
+if len(sys.argv) > 1 and sys.argv[1] == "sparse":  # few rays per voxel: is the 8 N / G bound on the copies right?
+    CASES = [("lens 64^3, 256^2", 64, 2, sc.field_luneburg, lambda: sc.rays_collimated(256)),
+             ("bump 64^3, 256^2", 64, 2, sc.field_bump, lambda: sc.rays_collimated(256)),
+             ("one view 65^3, 64^2 x 16", 65, 2, sc.field_bump, lambda: multiview_rays(1, 64, 16)),
+             ("lens 128^3, 512^2", 128, 2, sc.field_luneburg, lambda: sc.rays_collimated(512)),
+             ("bump 128^3, 512^2", 128, 2, sc.field_bump, lambda: sc.rays_collimated(512))]
 if len(sys.argv) > 1 and sys.argv[1] == "big":
     CASES = []
 if len(sys.argv) > 1 and sys.argv[1] in ("all", "big"):
