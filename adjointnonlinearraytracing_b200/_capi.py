@@ -26,6 +26,8 @@ DRRT_NO_FACE_CARRY = 1 << 7
 DRRT_AUTO_INTERLEAVE = 1 << 18
 DRRT_NO_REPLICAS = 1 << 19
 DRRT_FACE_CARRY = 1 << 24
+DRRT_PAIR_RAYS = 1 << 25
+DRRT_NO_PAIR_RAYS = 1 << 26
 DRRT_AGG_RUN_WARP = 15 << 8
 
 

@@ -118,6 +118,14 @@ int arith_of(unsigned flags) {
   return 2;
 }  // max_bits word, padded
 
+// Two rays per thread in drrt_trace (trace_pair_kernel): forced by DRRT_PAIR_RAYS / DRRT_NO_PAIR_RAYS.
+int pair_of(unsigned flags, int64_t N) {
+  if (flags & DRRT_NO_PAIR_RAYS) return 0;
+  if (flags & DRRT_PAIR_RAYS) return 1;
+  (void) N;
+  return 0;
+}
+
 int trace_common(int kind, const float *rif, const float *sdf, int W, int H, int D,
                  const float *pos, const float *vel, const float *aux0, const float *aux1,
                  int64_t N, int layout, float h, float ds, float *xt, float *vt,
@@ -145,6 +153,8 @@ int trace_common(int kind, const float *rif, const float *sdf, int W, int H, int
     a.tail_max_iters = a.tail_iters + N;
     CU_TRY(cudaMemsetAsync(a.tail_max_iters, 0, sizeof(int), s));
   }
+  a.pair = pair_of(flags, N);
+  a.one = 1.0f;
   g_launches += launch_trace(kind, arith_of(flags), a, s);
   rc = check_launch("trace");
   if (tail) cudaFreeAsync(tail, s);

@@ -270,6 +270,55 @@ __device__ __forceinline__ void eval_grad_ref_x2(const GridP &g, const f32x2 V[4
   nx.x = mul_(gx, g.rcp_h); nx.y = mul_(gy, g.rcp_h); nx.z = mul_(gz, g.rcp_h);
 }
 
+// ---------------------------------------------------------------------------
+// Two rays per thread ("ray pairs"): ray A in the low half and ray B in the high
+// half of every f32x2, so that ALL of the literal arithmetic -- multiplies and
+// adds -- issues as packed FP32 (one FMUL2 / FFMA2 per two rays).  Adds are
+// written as fma(a, 1, b), which rounds exactly like add.rn (a * 1 is exact), with
+// the 1 passed in from the host as an opaque kernel argument so that ptxas can
+// neither fold it nor contract a producing multiply into the add.
+// ---------------------------------------------------------------------------
+struct PairK {
+  f32x2 one, mone;  // (1, 1), (-1, -1)
+  __device__ __forceinline__ f32x2 add(f32x2 a, f32x2 b) const { return fma2(a, one, b); }    // a + b
+  __device__ __forceinline__ f32x2 sub(f32x2 a, f32x2 b) const { return fma2(b, mone, a); }   // a - b
+};
+
+// volume::eval_grad, src/volume.cpp:152-178, for two rays at once: the same
+// operations in the same order with the same roundings as eval_grad_ref.
+// Vp[k] = (corner k of ray A's cell, corner k of ray B's cell), reference corner order.
+__device__ __forceinline__ void eval_grad_ref_pair(const PairK &K, f32x2 rcp_h, const f32x2 Vp[8], f32x2 w0x,
+                                                   f32x2 w0y, f32x2 w0z, f32x2 &n, f32x2 nx[3]) {
+  const f32x2 w1x = K.sub(K.one, w0x), w1y = K.sub(K.one, w0y), w1z = K.sub(K.one, w0z);
+  {
+    const f32x2 p00 = mul2(w1x, w1y), p10 = mul2(w0x, w1y), p01 = mul2(w1x, w0y), p11 = mul2(w0x, w0y);
+    f32x2 s = mul2(mul2(p00, w1z), Vp[0]);
+    s = K.add(s, mul2(mul2(p10, w1z), Vp[1]));
+    s = K.add(s, mul2(mul2(p01, w1z), Vp[2]));
+    s = K.add(s, mul2(mul2(p11, w1z), Vp[3]));
+    s = K.add(s, mul2(mul2(p00, w0z), Vp[4]));
+    s = K.add(s, mul2(mul2(p10, w0z), Vp[5]));
+    s = K.add(s, mul2(mul2(p01, w0z), Vp[6]));
+    s = K.add(s, mul2(mul2(p11, w0z), Vp[7]));
+    n = s;
+  }
+#define DRRT_Q2(va, wa, wb) mul2(mul2(va, wa), wb)
+#define DRRT_S42(a, b, c, d) K.add(K.add(K.add(a, b), c), d)
+  const f32x2 gx = K.sub(DRRT_S42(DRRT_Q2(Vp[1], w1y, w1z), DRRT_Q2(Vp[5], w1y, w0z), DRRT_Q2(Vp[3], w0y, w1z), DRRT_Q2(Vp[7], w0y, w0z)),
+                         DRRT_S42(DRRT_Q2(Vp[0], w1y, w1z), DRRT_Q2(Vp[4], w1y, w0z), DRRT_Q2(Vp[2], w0y, w1z), DRRT_Q2(Vp[6], w0y, w0z)));
+  // d/dy and d/dz share the first products v * wx
+  f32x2 F[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) F[k] = mul2(Vp[k], (k & 1) ? w0x : w1x);
+  const f32x2 gy = K.sub(DRRT_S42(mul2(F[2], w1z), mul2(F[6], w0z), mul2(F[3], w1z), mul2(F[7], w0z)),
+                         DRRT_S42(mul2(F[0], w1z), mul2(F[4], w0z), mul2(F[1], w1z), mul2(F[5], w0z)));
+  const f32x2 gz = K.sub(DRRT_S42(mul2(F[4], w1y), mul2(F[6], w0y), mul2(F[5], w1y), mul2(F[7], w0y)),
+                         DRRT_S42(mul2(F[0], w1y), mul2(F[2], w0y), mul2(F[1], w1y), mul2(F[3], w0y)));
+#undef DRRT_Q2
+#undef DRRT_S42
+  nx[0] = mul2(gx, rcp_h); nx[1] = mul2(gy, rcp_h); nx[2] = mul2(gz, rcp_h);
+}
+
 // enoki lerp(a,b,t) = fmadd(b, t, fnmadd(a, t, a))
 __device__ __forceinline__ float lerp_ref(float a, float b, float t) { return fma_(b, t, fma_(-a, t, a)); }
 

@@ -253,6 +253,142 @@ __global__ void __launch_bounds__(kTraceThreads, KIND == K_PLAIN ? kTraceMinBloc
   }
 }
 
+// ---------------------------------------------------------------------------
+// Forward trace, two rays per thread (Tracer::trace only, literal arithmetic).
+// trace_kernel is bound by instruction issue, and two thirds of its instructions are
+// the float32 operations of the reference formulas; with ray A in the low and ray B in
+// the high half of every f32x2 each of them -- multiplies and adds alike -- issues once
+// for two rays (FMUL2 / FFMA2, see PairK).  Everything that is per ray stays per ray: the
+// cell cache tags and refills, the in-bounds tests and the exit, so the results are
+// bit-identical to trace_kernel<K_PLAIN, A_REF>.  Lane l of warp w takes rays 64 w + l and
+// 64 w + 32 + l (same coalescing as one ray per lane; neighbours in the batch, so the two
+// rays of a thread enter and leave the volume within a few steps of each other).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ f32x2 with_lo(f32x2 v, float lo) { return pk2(lo, hi2(v)); }
+__device__ __forceinline__ f32x2 with_hi(f32x2 v, float hi) { return pk2(lo2(v), hi); }
+__device__ __forceinline__ f3 lo3(const f32x2 p[3]) { f3 r = {lo2(p[0]), lo2(p[1]), lo2(p[2])}; return r; }
+__device__ __forceinline__ f3 hi3(const f32x2 p[3]) { f3 r = {hi2(p[0]), hi2(p[1]), hi2(p[2])}; return r; }
+
+// A ray of the pair has left the loop: write its outputs (src/tracer.cpp:79-80, :95).
+__device__ __forceinline__ void pair_store_exit(const TraceArgs &a, int64_t r, bool crossed, f3 x, f3 v) {
+  if (crossed) {
+    st3(a.xt, r, a.N, a.layout, x);
+    st3(a.vt, r, a.N, a.layout, v);
+  } else {  // escaped without ever having been inside: the launch state is returned
+    st3(a.xt, r, a.N, a.layout, ld3(a.pos, r, a.N, a.layout));
+    st3(a.vt, r, a.N, a.layout, ld3(a.vel, r, a.N, a.layout));
+  }
+}
+
+__global__ void __launch_bounds__(kTraceThreads, kTracePairMinBlocks) trace_pair_kernel(TraceArgs a) {
+  const unsigned lane = threadIdx.x & 31;
+  const int64_t gw = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t rA = gw * 64 + lane, rB = rA + 32;
+  const GridP g = a.grid;
+  PairK K;
+  K.one = pk2(a.one, a.one);
+  K.mone = pk2(-a.one, -a.one);
+  const f32x2 DS = pk2(a.ds, a.ds), RH = pk2(g.rcp_h, g.rcp_h);
+  bool liveA = rA < a.N, liveB = rB < a.N;
+  f32x2 X[3] = {0ull, 0ull, 0ull}, V[3] = {0ull, 0ull, 0ull};
+  if (liveA) {
+    const f3 x = ld3(a.pos, rA, a.N, a.layout), v = ld3(a.vel, rA, a.N, a.layout);
+    X[0] = with_lo(X[0], x.x); X[1] = with_lo(X[1], x.y); X[2] = with_lo(X[2], x.z);
+    V[0] = with_lo(V[0], v.x); V[1] = with_lo(V[1], v.y); V[2] = with_lo(V[2], v.z);
+  }
+  if (liveB) {
+    const f3 x = ld3(a.pos, rB, a.N, a.layout), v = ld3(a.vel, rB, a.N, a.layout);
+    X[0] = with_hi(X[0], x.x); X[1] = with_hi(X[1], x.y); X[2] = with_hi(X[2], x.z);
+    V[0] = with_hi(V[0], v.x); V[1] = with_hi(V[1], v.y); V[2] = with_hi(V[2], v.z);
+  }
+  bool insA = liveA && inbounds(g, lo3(X)), insB = liveB && inbounds(g, hi3(X));  // :61
+  int stepsA = 0, stepsB = 0;
+  CellTag tagA, tagB;
+  tagA.reset(); tagB.reset();
+  f32x2 Vp[8] = {0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull};
+  int i = 0;
+  while ((liveA | liveB) && i < a.max_steps) {
+    if (insA | insB) {  // masked gather: outside rays see n = 0, grad n = 0 and fly straight
+      const f32x2 px = mul2(X[0], RH), py = mul2(X[1], RH), pz = mul2(X[2], RH);
+      CellIdx cA, cB;
+      cA.fx = floorf(lo2(px)); cA.fy = floorf(lo2(py)); cA.fz = floorf(lo2(pz));
+      cB.fx = floorf(hi2(px)); cB.fy = floorf(hi2(py)); cB.fz = floorf(hi2(pz));
+      const f32x2 wx = K.sub(px, pk2(cA.fx, cB.fx)), wy = K.sub(py, pk2(cA.fy, cB.fy)), wz = K.sub(pz, pk2(cA.fz, cB.fz));
+      if (insA && tagA.differs(cA)) {
+        tagA.set(cA);
+        f32x2 T[4];
+        gather_cell(g, cA.cx(), cA.cy(), cA.cz(), T);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { Vp[2 * j] = with_lo(Vp[2 * j], lo2(T[j])); Vp[2 * j + 1] = with_lo(Vp[2 * j + 1], hi2(T[j])); }
+      }
+      if (insB && tagB.differs(cB)) {
+        tagB.set(cB);
+        f32x2 T[4];
+        gather_cell(g, cB.cx(), cB.cy(), cB.cz(), T);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { Vp[2 * j] = with_hi(Vp[2 * j], lo2(T[j])); Vp[2 * j + 1] = with_hi(Vp[2 * j + 1], hi2(T[j])); }
+      }
+      f32x2 n, nx[3];
+      eval_grad_ref_pair(K, RH, Vp, wx, wy, wz, n, nx);
+      const f32x2 dsn = mul2(DS, n);
+      const f32x2 n0 = fma2(dsn, nx[0], V[0]), n1 = fma2(dsn, nx[1], V[1]), n2 = fma2(dsn, nx[2], V[2]);  // :70
+      if (insA & insB) {
+        V[0] = n0; V[1] = n1; V[2] = n2;
+      } else if (insA) {
+        V[0] = with_lo(V[0], lo2(n0)); V[1] = with_lo(V[1], lo2(n1)); V[2] = with_lo(V[2], lo2(n2));
+      } else {
+        V[0] = with_hi(V[0], hi2(n0)); V[1] = with_hi(V[1], hi2(n1)); V[2] = with_hi(V[2], hi2(n2));
+      }
+    }
+    X[0] = fma2(DS, V[0], X[0]); X[1] = fma2(DS, V[1], X[1]); X[2] = fma2(DS, V[2], X[2]);  // :71
+    ++i;
+    const bool inbA = inbounds(g, lo3(X)), inbB = inbounds(g, hi3(X));
+    if (inbA & inbB & liveA & liveB) {
+      insA = insB = true;  // :86 (fast path: nothing can end a ray while it stays inside)
+    } else {
+      if (liveA) {
+        if (!inbA) {
+          const bool crossed = insA;  // :74
+          if (crossed || escaped(g, lo3(X), lo3(V))) {  // :75-80
+            pair_store_exit(a, rA, crossed, lo3(X), lo3(V));
+            liveA = false; stepsA = i;
+          }
+        }
+        insA = liveA & inbA;
+      }
+      if (liveB) {
+        if (!inbB) {
+          const bool crossed = insB;
+          if (crossed || escaped(g, hi3(X), hi3(V))) {
+            pair_store_exit(a, rB, crossed, hi3(X), hi3(V));
+            liveB = false; stepsB = i;
+          }
+        }
+        insB = liveB & inbB;
+      }
+    }
+  }
+  int not_exited = 0;
+  if (liveA) {  // :89-96: current x, launch v
+    st3(a.xt, rA, a.N, a.layout, lo3(X));
+    st3(a.vt, rA, a.N, a.layout, ld3(a.vel, rA, a.N, a.layout));
+    stepsA = i; ++not_exited;
+  }
+  if (liveB) {
+    st3(a.xt, rB, a.N, a.layout, hi3(X));
+    st3(a.vt, rB, a.N, a.layout, ld3(a.vel, rB, a.N, a.layout));
+    stepsB = i; ++not_exited;
+  }
+  if (a.stats) {
+    const int64_t wsteps = warp_sum_i64((int64_t) stepsA + (int64_t) stepsB);
+    int ne = __reduce_add_sync(0xffffffffu, not_exited);
+    if (lane == 0) {
+      if (wsteps) atomicAdd((unsigned long long *) a.stats, (unsigned long long) wsteps);
+      if (ne) atomicAdd((unsigned long long *) a.stats + 1, (unsigned long long) ne);
+    }
+  }
+}
+
 // trace_target couples rays: the reference keeps testing every ray for a new
 // closest approach until the whole batch has escaped (src/tracer.cpp:216-231),
 // so an already-escaped ray's result depends on how long the slowest ray keeps
@@ -730,6 +866,10 @@ static void launch_trace_kind(int arith, const TraceArgs &a, cudaStream_t s) {
   const int nt = kTraceThreads;  // 32 / 64 / 128 threads per CTA time the same, also below one wave (profiles/r09_cta_size.log)
   unsigned nb = blocks_for(a.N, nt);
   // the forward pass is all trajectory: A_EXACT and A_REF are the same kernel
+  if (KIND == K_PLAIN && arith != A_FAST && a.pair) {
+    trace_pair_kernel<<<blocks_for(((a.N + 63) / 64) * 32, nt), nt, 0, s>>>(a);
+    return;
+  }
   if (arith == A_FAST) trace_kernel<KIND, A_FAST><<<nb, nt, 0, s>>>(a);
   else trace_kernel<KIND, A_REF><<<nb, nt, 0, s>>>(a);
 }

@@ -27,6 +27,10 @@ constexpr int kAdjThreads = DRRT_ADJ_THREADS;
 #ifndef DRRT_TRACE_MIN_BLOCKS
 #define DRRT_TRACE_MIN_BLOCKS 6  // measured (profiles/r06_tune_occupancy.log): 74 registers / 6 CTAs beat 56 / 9
 #endif
+#ifndef DRRT_TRACE_PAIR_MIN_BLOCKS
+#define DRRT_TRACE_PAIR_MIN_BLOCKS 4
+#endif
+constexpr int kTracePairMinBlocks = DRRT_TRACE_PAIR_MIN_BLOCKS;
 constexpr int kAdjMinBlocks = DRRT_ADJ_MIN_BLOCKS;
 constexpr int kTraceMinBlocks = DRRT_TRACE_MIN_BLOCKS;
 
@@ -46,6 +50,8 @@ struct TraceArgs {
   // trace_target tail state (SoA scratch)
   float *tail_x, *tail_v;
   int *tail_iters, *tail_max_iters;
+  int pair;   // trace only: two rays per thread (trace_pair_kernel)
+  float one;  // 1.0f, opaque to the compiler (PairK)
 };
 
 struct AdjArgs {

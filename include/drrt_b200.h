@@ -94,6 +94,12 @@ enum {
   DRRT_NO_REPLICAS = 1u << 19,
   /* bits 20-23  DRRT_REPLICAS(n), n in 2..15: force n gradient copies whatever the grid size
    *             (a beam focused inside a LARGE grid; the scratch buffer grows to (n-1) grids). */
+  /* drrt_trace only (literal arithmetic): DRRT_PAIR_RAYS traces two rays per thread so that every
+   * float32 operation of the reference formulas issues as packed FP32 (FMUL2 / FFMA2, one instruction
+   * per two rays; results bit-identical to one ray per thread); DRRT_NO_PAIR_RAYS forces one ray per
+   * thread.  Neither bit: the library's choice ("Ray pairs"). */
+  DRRT_PAIR_RAYS = 1u << 25,
+  DRRT_NO_PAIR_RAYS = 1u << 26,
   /* Adjoint only: accumulate the gradient in 64-bit fixed point so the result is
    * bit-stable from run to run regardless of atomic ordering (and of the ray
    * order / interleave). */
