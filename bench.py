@@ -384,6 +384,23 @@ def run_ours(args):
                               "live kernel time; peaks from profiles/r05_l2_probe.log", "source": pk["source"]}
             except Exception:
                 l2 = None
+        # what actually bounds the kernels at 256^3: instruction issue / the FP32 pipes.
+        # warp instructions per launch from the committed ncu capture of this workload over the live kernel
+        # times, against 4 schedulers x 1 instruction per clock per SM at the SM clock sampled during the run.
+        issue = None
+        ip = os.path.join(ROOT, "profiles", "issue_counts.json")
+        if os.path.exists(ip) and NG == 256 and clocks and clocks.get("sm_mhz"):
+            try:
+                ic = json.load(open(ip))
+                pk_inst = 148 * 4 * clocks["sm_mhz"] * 1e6 / 1e9
+                fi = ic["trace_kernel_warp_inst_per_launch"] / (fwd_ms * 1e-3) / 1e9
+                ai = ic["backtrace_kernel_warp_inst_per_launch"] / (adj_ms * 1e-3) / 1e9
+                issue = {"unit": "G warp-instructions/s", "peak": pk_inst,
+                         "fwd": {"achieved": fi, "frac": fi / pk_inst, "pipes_pct": ic["trace_kernel_pipes_pct"]},
+                         "adj": {"achieved": ai, "frac": ai / pk_inst, "pipes_pct": ic["backtrace_kernel_pipes_pct"]},
+                         "source": ic["source"]}
+            except Exception:
+                issue = None
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
@@ -402,7 +419,7 @@ def run_ours(args):
             "roofline": {
                 "bound": "hbm", "kernel": "backtrace_kernel<sdf=0,A_EXACT,AccumFloat> (face-carry flush, no interleave)", "achieved": adj_gbs, "peak": peak,
                 "unit": "GB/s", "frac": adj_gbs / peak, "traffic": traffic, "peak_source": peak_src,
-                "algorithmic_bytes_per_ray_step": BYTES_ADJ, "l2": l2,
+                "algorithmic_bytes_per_ray_step": BYTES_ADJ, "l2": l2, "issue": issue,
                 "fwd_kernel": {"achieved": fwd_gbs, "frac": fwd_gbs / peak, "algorithmic_bytes_per_ray_step": BYTES_FWD},
                 "step": {"achieved": (BYTES_FWD * s_f + BYTES_ADJ * s_b) / ((fwd_ms + adj_ms) * 1e-3) / 1e9,
                          "frac": (BYTES_FWD * s_f + BYTES_ADJ * s_b) / ((fwd_ms + adj_ms) * 1e-3) / 1e9 / peak},
