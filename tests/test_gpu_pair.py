@@ -98,3 +98,32 @@ def test_pair_full_size_matches(cuda_lib):
     h = float(sc.grid_spacing(ng)); ds = h / 2
     pos, vel = sc.rays_cone(s, spread=0.05, backoff=0.37 * ds)
     _both(ops, rif, torch.from_numpy(pos).cuda(), torch.from_numpy(vel).cuda(), h, ds)
+
+
+def test_pair_guard_bands(cuda_lib):
+    """Outputs of a ragged batch (the last thread has one ray or none, the last warp is partial) end exactly
+    where they should: sentinel bands around xt / vt stay untouched, in both layouts, through the C ABI."""
+    from ctypes import c_void_p
+    from adjointnonlinearraytracing_b200 import _capi, ops, scenes as sc
+    lib = _capi.load()
+    ng = 19
+    rif = torch.from_numpy(sc.field_bump(ng)).cuda()
+    h = float(sc.grid_spacing(ng)); ds = h / 2
+    pos, vel = sc.rays_cone(40, spread=0.3, backoff=0.37 * ds)
+    pos, vel = torch.from_numpy(pos).cuda(), torch.from_numpy(vel).cuda()
+    P = lambda t, off=0: c_void_p(t.data_ptr() + off)
+    pad = 1024
+    for n in (1, 31, 32, 33, 63, 64, 65, 97, 1599):
+        for lay in (3, 1):
+            p = pos[:n].contiguous() if lay == 3 else pos[:n].t().contiguous()
+            v = vel[:n].contiguous() if lay == 3 else vel[:n].t().contiguous()
+            ref_x, ref_v = ops.trace(rif, p, v, h, ds, flags=NOPAIR, layout="aos" if lay == 3 else "soa")
+            xb = torch.full((3 * n + 2 * pad,), 7.5, device="cuda")
+            vb = torch.full((3 * n + 2 * pad,), -3.25, device="cuda")
+            rc = lib.drrt_trace(P(rif), ng, ng, ng, P(p), P(v), n, lay, h, ds, P(xb, 4 * pad), P(vb, 4 * pad),
+                                c_void_p(0), PAIR, c_void_p(torch.cuda.current_stream().cuda_stream))
+            assert rc == 0
+            torch.cuda.synchronize()
+            assert bool((xb[:pad] == 7.5).all()) and bool((xb[-pad:] == 7.5).all())
+            assert bool((vb[:pad] == -3.25).all()) and bool((vb[-pad:] == -3.25).all())
+            assert _same(xb[pad:-pad].view_as(ref_x), ref_x) and _same(vb[pad:-pad].view_as(ref_v), ref_v)
