@@ -65,6 +65,7 @@ PROTOTYPES = {
     "drrt_cylinder_eval": (c_int, [_P, _I, _F, _F, _P, _L, _I, _P, _P, _P, _P]),
     "drrt_cylinder_splat": (c_int, [_P, _I, _F, _F, _P, _P, _P, _L, _I, _P]),
     "drrt_adam_step": (c_int, [_P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _F, _F, _F, _U, _P]),
+    "drrt_adam_step_slab": (c_int, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _F, _F, _F, _F, _U, _P]),
     "drrt_upres_volume": (c_int, [_P, _I, _I, _I, _P, _I, _I, _I, _P]),
     "drrt_sensor_splat": (c_int, [_P, _P, _P, _F, _L, _I, _P, _P, _P, _P, _I, _F, _P, _U, _P]),
     "drrt_sensor_splat_backward": (c_int, [_P, _P, _P, _F, _L, _I, _P, _P, _P, _P, _I, _F, _P, _P, _P, _P, _U, _P]),
@@ -81,6 +82,8 @@ PROTOTYPES = {
     "drrt_comm_init_rank": (c_int, [POINTER(c_void_p), _I, _P, _I]),
     "drrt_comm_destroy": (c_int, [_P]),
     "drrt_allreduce_grad": (c_int, [_P, c_size_t, _P, _P]),
+    "drrt_reduce_scatter_grad": (c_int, [_P, c_size_t, _I, _P, _P]),
+    "drrt_allgather_grid": (c_int, [_P, c_size_t, _I, _P, _P]),
 }
 
 _lib = None

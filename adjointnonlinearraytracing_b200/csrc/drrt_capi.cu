@@ -502,17 +502,28 @@ int drrt_plane_source_rand(const float *offset, uint64_t seed, const float *view
                           independent, post_rot, post_span, x, v, planes, keep, nullptr, nullptr, stream);
 }
 
-int drrt_adam_step(float *n, const float *grad, float *exp_avg, float *exp_avg_sq, int S0, int S1, int S2,
-                   int step, float lr, float beta1, float beta2, float eps, float clamp_min,
-                   unsigned flags, drrt_stream_t stream) {
+int drrt_adam_step_slab(float *n, const float *grad, float *exp_avg, float *exp_avg_sq, int S0, int S1, int S2,
+                        int i0_begin, int i0_count, int step, float lr, float beta1, float beta2, float eps,
+                        float clamp_min, unsigned flags, drrt_stream_t stream) {
   if (S0 <= 0 || S1 <= 0 || S2 <= 0) return fail(DRRT_ERR_RESOLUTION, "Resolution doesn't match data");
+  if (i0_begin < 0 || i0_count < 0 || (int64_t) i0_begin + i0_count > S0)
+    return fail(DRRT_ERR_RESOLUTION, "slab outside the grid");
+  if (i0_count == 0) return DRRT_OK;
   if (!n || !grad || !exp_avg || !exp_avg_sq) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL grid buffer");
   if (step < 1) return fail(DRRT_ERR_INVALID_ARGUMENT, "step counts from 1 (torch.optim.Adam)");
-  int r = launch_adam_step(n, grad, exp_avg, exp_avg_sq, S0, S1, S2, step, lr, beta1, beta2, eps, clamp_min,
-                           !(flags & DRRT_ADAM_KEEP_BOUNDARY), !(flags & DRRT_ADAM_NO_CLAMP), (cudaStream_t) stream);
+  int r = launch_adam_step(n, grad, exp_avg, exp_avg_sq, S0, S1, S2, i0_begin, i0_count, step, lr, beta1, beta2, eps,
+                           clamp_min, !(flags & DRRT_ADAM_KEEP_BOUNDARY), !(flags & DRRT_ADAM_NO_CLAMP),
+                           (cudaStream_t) stream);
   if (r < 0) return fail(DRRT_ERR_RESOLUTION, "grid too large for one launch");
   g_launches += r;
   return check_launch("adam_step");
+}
+
+int drrt_adam_step(float *n, const float *grad, float *exp_avg, float *exp_avg_sq, int S0, int S1, int S2,
+                   int step, float lr, float beta1, float beta2, float eps, float clamp_min,
+                   unsigned flags, drrt_stream_t stream) {
+  return drrt_adam_step_slab(n, grad, exp_avg, exp_avg_sq, S0, S1, S2, 0, S0, step, lr, beta1, beta2, eps, clamp_min,
+                             flags, stream);
 }
 
 int drrt_upres_volume(const float *src, int s0, int s1, int s2, float *dst, int d0, int d1, int d2,

@@ -171,6 +171,8 @@ typedef int (*fn_uid_t)(nccl_uid_t *);
 typedef int (*fn_init_t)(void **, int, nccl_uid_t, int);
 typedef int (*fn_destroy_t)(void *);
 typedef int (*fn_allreduce_t)(const void *, void *, size_t, int, int, void *, cudaStream_t);
+typedef int (*fn_reducescatter_t)(const void *, void *, size_t, int, int, void *, cudaStream_t);
+typedef int (*fn_allgather_t)(const void *, void *, size_t, int, void *, cudaStream_t);
 typedef const char *(*fn_errstr_t)(int);
 
 static struct {
@@ -180,6 +182,8 @@ static struct {
   fn_init_t init = nullptr;
   fn_destroy_t destroy = nullptr;
   fn_allreduce_t allreduce = nullptr;
+  fn_reducescatter_t reducescatter = nullptr;
+  fn_allgather_t allgather = nullptr;
   fn_errstr_t errstr = nullptr;
 } g_nccl;
 
@@ -195,6 +199,8 @@ static bool nccl_load() {
     g_nccl.init = (fn_init_t) dlsym(g_nccl.h, "ncclCommInitRank");
     g_nccl.destroy = (fn_destroy_t) dlsym(g_nccl.h, "ncclCommDestroy");
     g_nccl.allreduce = (fn_allreduce_t) dlsym(g_nccl.h, "ncclAllReduce");
+    g_nccl.reducescatter = (fn_reducescatter_t) dlsym(g_nccl.h, "ncclReduceScatter");
+    g_nccl.allgather = (fn_allgather_t) dlsym(g_nccl.h, "ncclAllGather");
     g_nccl.errstr = (fn_errstr_t) dlsym(g_nccl.h, "ncclGetErrorString");
   });
   return g_nccl.h && g_nccl.uid && g_nccl.init && g_nccl.destroy && g_nccl.allreduce;
@@ -236,6 +242,24 @@ int drrt_allreduce_grad(float *grad, size_t count, void *comm, drrt_stream_t str
   if (!nccl_load()) { set_err("libnccl.so.2 not found"); return DRRT_ERR_NCCL; }
   int rc = g_nccl.allreduce(grad, grad, count, 7, 0, comm, (cudaStream_t) stream);
   if (rc) return nccl_fail("ncclAllReduce", rc);
+  return DRRT_OK;
+}
+
+// Sharded optimiser step: in-place reduce-scatter of the private gradient grids
+// (recvbuff = sendbuff + rank * recvcount is NCCL's in-place form) and in-place all-gather of the updated slabs.
+int drrt_reduce_scatter_grad(float *grad, size_t slab_count, int rank, void *comm, drrt_stream_t stream) {
+  if (!nccl_load() || !g_nccl.reducescatter) { set_err("libnccl.so.2 not found"); return DRRT_ERR_NCCL; }
+  if (!grad || rank < 0) { set_err("reduce_scatter: bad argument"); return DRRT_ERR_INVALID_ARGUMENT; }
+  int rc = g_nccl.reducescatter(grad, grad + (size_t) rank * slab_count, slab_count, 7, 0, comm, (cudaStream_t) stream);
+  if (rc) return nccl_fail("ncclReduceScatter", rc);
+  return DRRT_OK;
+}
+
+int drrt_allgather_grid(float *grid, size_t slab_count, int rank, void *comm, drrt_stream_t stream) {
+  if (!nccl_load() || !g_nccl.allgather) { set_err("libnccl.so.2 not found"); return DRRT_ERR_NCCL; }
+  if (!grid || rank < 0) { set_err("allgather: bad argument"); return DRRT_ERR_INVALID_ARGUMENT; }
+  int rc = g_nccl.allgather(grid + (size_t) rank * slab_count, grid, slab_count, 7, comm, (cudaStream_t) stream);
+  if (rc) return nccl_fail("ncclAllGather", rc);
   return DRRT_OK;
 }
 

@@ -148,7 +148,9 @@ int launch_fixed_to_float(const unsigned long long *fixed, const unsigned *max_b
                           int64_t G, bool accumulate, cudaStream_t s);
 
 // optimiser step / up-res
-int launch_adam_step(float *n, const float *grad, float *m, float *v, int S0, int S1, int S2, int step,
+// the buffers hold planes [i0_begin, i0_begin + i0_count) of the (S0, S1, S2) grid
+int launch_adam_step(float *n, const float *grad, float *m, float *v, int S0, int S1, int S2, int i0_begin,
+                     int i0_count, int step,
                      float lr, float beta1, float beta2, float eps, float clamp_min, bool zero_boundary,
                      bool clamp, cudaStream_t s);
 int launch_upres_volume(const float *src, int s0, int s1, int s2, float *dst, int d0, int d1, int d2,

@@ -35,9 +35,11 @@ __device__ __forceinline__ void adam_one(float &n, float g, float &m, float &v, 
 template <int VEC>
 __global__ void __launch_bounds__(128) adam_step_kernel(float *__restrict__ n, const float *__restrict__ grad,
                                                         float *__restrict__ m, float *__restrict__ v, int S0,
-                                                        int S1, int S2, int bpr, AdamP p) {
-  const int row = blockIdx.x / bpr;  // i0 * S1 + i1
-  const int i0 = row / S1, i1 = row - i0 * S1;
+                                                        int S1, int S2, int i0_begin, int bpr, AdamP p) {
+  // the buffers hold planes [i0_begin, i0_begin + count) of an (S0, S1, S2) grid: the whole grid, or one
+  // rank's slab of the sharded optimiser step (boundary planes are those of the WHOLE grid)
+  const int row = blockIdx.x / bpr;  // (i0 - i0_begin) * S1 + i1
+  const int i0 = row / S1 + i0_begin, i1 = row - (row / S1) * S1;
   const int i2 = ((blockIdx.x - row * bpr) * blockDim.x + threadIdx.x) * VEC;
   if (i2 >= S2) return;
   const bool row_boundary = p.zero_boundary && (i0 == 0 || i0 == S0 - 1 || i1 == 0 || i1 == S1 - 1);
@@ -61,10 +63,11 @@ __global__ void __launch_bounds__(128) adam_step_kernel(float *__restrict__ n, c
   }
 }
 
-int launch_adam_step(float *n, const float *grad, float *m, float *v, int S0, int S1, int S2, int step,
+int launch_adam_step(float *n, const float *grad, float *m, float *v, int S0, int S1, int S2, int i0_begin,
+                     int i0_count, int step,
                      float lr, float beta1, float beta2, float eps, float clamp_min, bool zero_boundary,
                      bool clamp, cudaStream_t s) {
-  if ((int64_t) S0 * S1 * S2 <= 0) return 0;
+  if ((int64_t) i0_count * S1 * S2 <= 0) return 0;
   AdamP p;
   const double bc1 = 1.0 - pow((double) beta1, (double) step), bc2 = 1.0 - pow((double) beta2, (double) step);
   p.lr_over_bc1 = (float) ((double) lr / bc1);
@@ -73,10 +76,10 @@ int launch_adam_step(float *n, const float *grad, float *m, float *v, int S0, in
   p.zero_boundary = zero_boundary; p.clamp = clamp;
   const bool vec = (S2 % 4 == 0) && ((((uintptr_t) n | (uintptr_t) grad | (uintptr_t) m | (uintptr_t) v) & 15) == 0);
   const int bpr = (S2 / (vec ? 4 : 1) + 127) / 128;
-  const int64_t nblocks = (int64_t) S0 * S1 * bpr;
+  const int64_t nblocks = (int64_t) i0_count * S1 * bpr;
   if (nblocks > 0x7fffffffLL) return -1;
-  if (vec) adam_step_kernel<4><<<(unsigned) nblocks, 128, 0, s>>>(n, grad, m, v, S0, S1, S2, bpr, p);
-  else adam_step_kernel<1><<<(unsigned) nblocks, 128, 0, s>>>(n, grad, m, v, S0, S1, S2, bpr, p);
+  if (vec) adam_step_kernel<4><<<(unsigned) nblocks, 128, 0, s>>>(n, grad, m, v, S0, S1, S2, i0_begin, bpr, p);
+  else adam_step_kernel<1><<<(unsigned) nblocks, 128, 0, s>>>(n, grad, m, v, S0, S1, S2, i0_begin, bpr, p);
   return 1;
 }
 

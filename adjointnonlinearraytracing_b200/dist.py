@@ -83,6 +83,73 @@ class GradAllReduce:
             self.comm = None
 
 
+class ShardedAdam:
+    """The optimiser step of ``multires_opt`` (reference core/optimizer.py:61-68) split over the ranks by
+    slabs of the slowest grid axis (the 512^3 configuration):
+
+        reduce-scatter of the private gradient grids  ->  fused boundary-zero + Adam + clamp on this rank's slab
+        ->  all-gather of the updated slabs into every rank's replica of ``n``.
+
+    Same bytes on the wire as the all-reduce of ``GradAllReduce``, 1/world of the optimiser pass and of the Adam
+    state per rank.  Needs ``n.shape[0] % world == 0`` (equal slabs); ``step`` leaves every rank with the same grid:
+    the one ``ops.adam_step_`` produces from the summed gradient (the update is per voxel, so splitting it changes
+    nothing; only NCCL's summation order inside reduce-scatter vs all-reduce can differ in the last bit).
+    ``step_fn(n_slab, grad_slab, m_slab, v_slab, shape, i0_begin, step)`` replaces the CUDA kernel in the CPU
+    (gloo) tests of this host logic.
+    """
+
+    def __init__(self, n: torch.Tensor, lr: float, betas=(0.9, 0.999), eps: float = 1e-8, clamp_min: float = 1.0,
+                 allreduce: Optional[GradAllReduce] = None, step_fn=None):
+        if n.dim() != 3 or not n.is_contiguous():
+            raise RuntimeError("ShardedAdam: expected a contiguous 3-D grid")
+        self.ar = allreduce if allreduce is not None else GradAllReduce()
+        self.world, self.rank = self.ar.world, self.ar.rank
+        if n.shape[0] % self.world:
+            raise RuntimeError(f"ShardedAdam: {n.shape[0]} planes do not split into {self.world} equal slabs")
+        self.n = n
+        self.planes = n.shape[0] // self.world
+        self.i0 = self.rank * self.planes
+        self.lr, self.betas, self.eps, self.clamp_min = float(lr), tuple(betas), float(eps), float(clamp_min)
+        self.step_count = 0
+        slab = n[self.i0:self.i0 + self.planes]
+        self.exp_avg = torch.zeros_like(slab)
+        self.exp_avg_sq = torch.zeros_like(slab)
+        self.step_fn = step_fn
+
+    def _slab(self, t: torch.Tensor) -> torch.Tensor:
+        return t[self.i0:self.i0 + self.planes]
+
+    def step(self, grad: torch.Tensor) -> torch.Tensor:
+        """``grad``: this rank's private gradient grid (overwritten: scratch after the call).  Returns ``n``."""
+        if grad.shape != self.n.shape or not grad.is_contiguous():
+            raise RuntimeError("Resolution doesn't match data")
+        n = self.n
+        count = self.planes * n.shape[1] * n.shape[2]
+        native = self.world > 1 and self.ar.backend == "nccl-native"
+        if native:
+            stream = c_void_p(torch.cuda.current_stream(grad.device).cuda_stream)
+            _capi.check(_capi.load().drrt_reduce_scatter_grad(c_void_p(grad.data_ptr()), count, self.rank,
+                                                              self.ar.comm, stream))
+        elif self.world > 1:  # gloo has no reduce-scatter: sum everything, keep the slab
+            dist.all_reduce(grad, op=dist.ReduceOp.SUM, group=self.ar.group)
+        self.step_count += 1
+        with torch.no_grad():
+            args = (self._slab(n.detach()), self._slab(grad), self.exp_avg, self.exp_avg_sq, tuple(n.shape), self.i0,
+                    self.step_count)
+            if self.step_fn is not None:
+                self.step_fn(*args)
+            else:
+                ops.adam_step_slab_(*args, self.lr, self.betas, self.eps, clamp_min=self.clamp_min)
+            if native:
+                _capi.check(_capi.load().drrt_allgather_grid(c_void_p(n.data_ptr()), count, self.rank, self.ar.comm,
+                                                             stream))
+            elif self.world > 1:
+                parts = [torch.empty_like(self._slab(n.detach())) for _ in range(self.world)]
+                dist.all_gather(parts, self._slab(n.detach()).contiguous(), group=self.ar.group)
+                n.detach().copy_(torch.cat(parts, dim=0))
+        return n
+
+
 class ShardedTracer:
     """Forward + adjoint over this rank's ray block with the all-reduced gradient.
 

@@ -372,6 +372,27 @@ def adam_step_(n, grad, exp_avg, exp_avg_sq, step, lr, betas=(0.9, 0.999), eps=1
     return n
 
 
+def adam_step_slab_(n_slab, grad_slab, exp_avg_slab, exp_avg_sq_slab, shape, i0_begin, step, lr, betas=(0.9, 0.999),
+                    eps=1e-8, clamp_min=1.0, zero_boundary=True, clamp=True):
+    """``adam_step_`` on planes ``[i0_begin, i0_begin + n_slab.shape[0])`` of a grid of ``shape`` only (one rank's
+    share of the sharded optimiser step, ``dist.ShardedAdam``).  The four tensors are (views of) that slab; the
+    zeroed boundary is that of the whole grid."""
+    S0, S1, S2 = (int(s) for s in shape)
+    for name, t in (("n", n_slab), ("grad", grad_slab), ("exp_avg", exp_avg_slab), ("exp_avg_sq", exp_avg_sq_slab)):
+        if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise RuntimeError(f"{name}: expected a contiguous float32 CUDA tensor")
+        if t.dim() != 3 or tuple(t.shape[1:]) != (S1, S2) or t.shape[0] != n_slab.shape[0]:
+            raise RuntimeError("Resolution doesn't match data")
+    flags = (0 if zero_boundary else 1) | (0 if clamp else 2)
+    with torch.cuda.device(n_slab.device):
+        _capi.check(_capi.load().drrt_adam_step_slab(_ptr(n_slab), _ptr(grad_slab), _ptr(exp_avg_slab),
+                                                     _ptr(exp_avg_sq_slab), S0, S1, S2, int(i0_begin),
+                                                     int(n_slab.shape[0]), int(step), float(lr), float(betas[0]),
+                                                     float(betas[1]), float(eps), float(clamp_min), flags,
+                                                     _stream(n_slab)))
+    return n_slab
+
+
 def upres_volume(n, new_res):
     """``grid.upres_volume`` / ``optimizer.upres_scene`` (reference core/grid.py:318-330,
     core/optimizer.py:7-10): trilinear resample of a cubic grid to ``new_res``."""

@@ -225,6 +225,12 @@ enum { DRRT_ADAM_KEEP_BOUNDARY = 1u << 0, DRRT_ADAM_NO_CLAMP = 1u << 1 };
 int drrt_adam_step(float *n, const float *grad, float *exp_avg, float *exp_avg_sq, int S0, int S1, int S2,
                    int step, float lr, float beta1, float beta2, float eps, float clamp_min,
                    unsigned flags, drrt_stream_t stream);
+/* The same step on planes [i0_begin, i0_begin + i0_count) of the (S0,S1,S2) grid only: all four pointers address
+ * the FIRST element of that slab (each rank's share of the sharded optimiser step, see drrt_reduce_scatter_grad);
+ * the zeroed boundary is that of the whole grid. */
+int drrt_adam_step_slab(float *n, const float *grad, float *exp_avg, float *exp_avg_sq, int S0, int S1, int S2,
+                        int i0_begin, int i0_count, int step, float lr, float beta1, float beta2, float eps,
+                        float clamp_min, unsigned flags, drrt_stream_t stream);
 int drrt_upres_volume(const float *src, int s0, int s1, int s2, float *dst, int d0, int d1, int d2,
                       drrt_stream_t stream);
 
@@ -333,6 +339,14 @@ int drrt_comm_unique_id(char id[DRRT_UNIQUE_ID_BYTES]);
 int drrt_comm_init_rank(void **comm, int nranks, const char id[DRRT_UNIQUE_ID_BYTES], int rank);
 int drrt_comm_destroy(void *comm);
 int drrt_allreduce_grad(float *grad, size_t count, void *comm, drrt_stream_t stream);
+/* Sharded optimiser step for grids whose Adam pass is worth splitting (the 512^3
+ * configuration): the same bytes on the wire as the all-reduce, 1/nranks of the optimiser work and state.
+ *   drrt_reduce_scatter_grad: in place; afterwards grad[rank * slab_count, (rank + 1) * slab_count) holds the
+ *                             sum over ranks of that slab (the rest of `grad` is scratch).  count = nranks * slab_count.
+ *   drrt_adam_step_slab       on that slab (above), then
+ *   drrt_allgather_grid:      in place; every rank contributes grid[rank * slab_count, ...) and receives the rest. */
+int drrt_reduce_scatter_grad(float *grad, size_t slab_count, int rank, void *comm, drrt_stream_t stream);
+int drrt_allgather_grid(float *grid, size_t slab_count, int rank, void *comm, drrt_stream_t stream);
 
 #ifdef __cplusplus
 }

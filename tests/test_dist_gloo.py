@@ -78,3 +78,57 @@ def test_two_rank_gradient_allreduce_matches_single_batch(tmp_path, oracle_mod):
     # forward outputs stay sharded: concatenating the shards gives the single-batch result
     xs = np.concatenate([np.load(tmp_path / "xt0.npy"), np.load(tmp_path / "xt1.npy")])
     assert np.array_equal(xs, xt)
+
+
+def _adam_worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import optim_oracle as oo
+        from adjointnonlinearraytracing_b200.dist import ShardedAdam
+        rng = np.random.default_rng(3)
+        shape = (8, 5, 6)
+        n0 = (1.0 + 0.2 * rng.random(shape)).astype(np.float32)
+        grads = [[rng.standard_normal(shape).astype(np.float32) for _ in range(world)] for _ in range(3)]
+
+        def step_fn(n_slab, g_slab, m_slab, v_slab, full_shape, i0, step):
+            # the CPU restatement on the WHOLE grid (it owns the boundary mask), cut back to this slab
+            k = n_slab.shape[0]
+            pad = lambda t: np.concatenate([np.zeros((i0,) + t.shape[1:], np.float32), t.numpy(),
+                                            np.zeros((full_shape[0] - i0 - k,) + t.shape[1:], np.float32)])
+            out, m, v = oo.adam_step(pad(n_slab), pad(g_slab), pad(m_slab), pad(v_slab), step, lr=1e-2)
+            n_slab.copy_(torch.from_numpy(out[i0:i0 + k])); m_slab.copy_(torch.from_numpy(m[i0:i0 + k]))
+            v_slab.copy_(torch.from_numpy(v[i0:i0 + k]))
+
+        n = torch.from_numpy(n0.copy())
+        opt = ShardedAdam(n, 1e-2, step_fn=step_fn)
+        assert opt.world == world and opt.planes == shape[0] // world and opt.i0 == rank * opt.planes
+        assert opt.exp_avg.shape == (shape[0] // world,) + shape[1:]
+        for it in range(3):
+            opt.step(torch.from_numpy(grads[it][rank].copy()))
+        np.save(os.path.join(out_dir, f"n{rank}.npy"), n.numpy())
+        bad = torch.zeros(7, 5, 6)
+        try:
+            ShardedAdam(bad, 1e-2, step_fn=step_fn)
+            raise AssertionError("7 planes over 2 ranks must be refused")
+        except RuntimeError:
+            pass
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_sharded_adam_matches_single_process(tmp_path, oracle_mod):
+    world = 2
+    mp.spawn(_adam_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    from oracle import optim_oracle as oo
+    rng = np.random.default_rng(3)
+    shape = (8, 5, 6)
+    n = (1.0 + 0.2 * rng.random(shape)).astype(np.float32)
+    grads = [[rng.standard_normal(shape).astype(np.float32) for _ in range(world)] for _ in range(3)]
+    m = np.zeros(shape, np.float32); v = np.zeros(shape, np.float32)
+    for it in range(3):
+        n, m, v = oo.adam_step(n, grads[it][0] + grads[it][1], m, v, it + 1, lr=1e-2)
+    n0 = np.load(tmp_path / "n0.npy"); n1 = np.load(tmp_path / "n1.npy")
+    assert np.array_equal(n0, n1)  # every rank holds the same updated grid
+    assert np.array_equal(n0, n)   # and it is the single-process result

@@ -116,3 +116,81 @@ def test_adam_step_full_size_properties(cuda_lib):
     pa.grad = ga.clone(); pa.grad[mk] = 0; oa.step()
     ops.adam_step_(a, ga, ma, va, 1, 1e-2, clamp=False)
     assert float((a - pa.detach()).abs().max()) <= 2e-6
+
+
+@pytest.mark.gpu
+def test_adam_step_slab_equals_whole_grid(cuda_lib):
+    """Any split of the grid into slabs of the slowest axis, stepped slab by slab, gives the bits of the one-pass
+    step (the boundary that is zeroed is the whole grid's), for vectorised and odd shapes."""
+    from adjointnonlinearraytracing_b200 import ops
+    gen = torch.Generator(device="cuda").manual_seed(11)
+    for shape, cuts in (((16, 12, 20), (0, 4, 8, 12, 16)), ((9, 7, 5), (0, 1, 2, 8, 9)), ((6, 4, 8), (0, 6))):
+        n = 1.0 + 0.3 * torch.rand(shape, device="cuda", generator=gen)
+        m = torch.rand(shape, device="cuda", generator=gen) * 0.1
+        v = torch.rand(shape, device="cuda", generator=gen) * 0.01
+        g = torch.randn(shape, device="cuda", generator=gen)
+        for kw in ({}, {"zero_boundary": False}, {"clamp": False}):
+            a, am, av = n.clone(), m.clone(), v.clone()
+            ops.adam_step_(a, g, am, av, 3, 1e-2, **kw)
+            b, bm, bv = n.clone(), m.clone(), v.clone()
+            for lo, hi in zip(cuts[:-1], cuts[1:]):
+                ops.adam_step_slab_(b[lo:hi], g[lo:hi], bm[lo:hi], bv[lo:hi], shape, lo, 3, 1e-2, **kw)
+            assert torch.equal(a, b) and torch.equal(am, bm) and torch.equal(av, bv)
+    lib_err = None
+    try:
+        ops.adam_step_slab_(n[0:2], g[0:2], m[0:2], v[0:2], (6, 4, 8), 5, 1, 1e-2)  # planes 5..6 of 6
+    except RuntimeError as e:
+        lib_err = str(e)
+    assert lib_err and "slab" in lib_err
+
+
+def _nccl_adam_worker(rank, world, port, out_dir):
+    import os, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from adjointnonlinearraytracing_b200 import ops
+        from adjointnonlinearraytracing_b200.dist import GradAllReduce, ShardedAdam
+        shape = (32, 20, 24)
+        gen = torch.Generator(device="cuda").manual_seed(7)  # same stream of numbers on every rank
+        n0 = 1.0 + 0.2 * torch.rand(shape, device="cuda", generator=gen)
+        grads = [[torch.randn(shape, device="cuda", generator=gen) for _ in range(world)] for _ in range(3)]
+        ar = GradAllReduce()
+        assert ar.backend == "nccl-native"
+        n = n0.clone()
+        opt = ShardedAdam(n, 1e-2, allreduce=ar)
+        ref = n0.clone(); m = torch.zeros_like(ref); v = torch.zeros_like(ref)
+        for it in range(3):
+            opt.step(grads[it][rank].clone())
+            summed = ar(grads[it][rank].clone())
+            ops.adam_step_(ref, summed, m, v, it + 1, 1e-2)
+        torch.cuda.synchronize()
+        err = float((n - ref).abs().max())
+        lo, hi = opt.i0, opt.i0 + opt.planes
+        merr = float((opt.exp_avg - m[lo:hi]).abs().max())
+        np.save(os.path.join(out_dir, f"n{rank}.npy"), n.cpu().numpy())
+        np.save(os.path.join(out_dir, f"err{rank}.npy"), np.array([err, merr]))
+        ar.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_sharded_adam_two_gpus_nccl(cuda_lib, tmp_path):
+    """reduce-scatter -> slab Adam -> all-gather over NCCL against all-reduce -> whole-grid Adam (needs 2 GPUs)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import socket
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+    mp.spawn(_nccl_adam_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    n0 = np.load(tmp_path / "n0.npy"); n1 = np.load(tmp_path / "n1.npy")
+    assert np.array_equal(n0, n1)
+    for r in range(2):
+        err, merr = np.load(tmp_path / f"err{r}.npy")
+        assert err <= 1e-6 and merr <= 1e-6, (r, err, merr)
