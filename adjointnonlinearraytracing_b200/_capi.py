@@ -43,6 +43,8 @@ def DRRT_INTERLEAVE(n: int) -> int:
     return int(n) << 12
 
 DRRT_UNIQUE_ID_BYTES = 128
+DRRT_IPC_HANDLE_BYTES = 64
+DRRT_MAX_PEERS = 16
 
 # every symbol include/drrt_b200.h declares (checked by tests/test_capi_symbols.py)
 _F, _I, _L, _U, _P = c_float, c_int, c_int64, c_uint, c_void_p
@@ -83,6 +85,10 @@ PROTOTYPES = {
     "drrt_comm_destroy": (c_int, [_P]),
     "drrt_allreduce_grad": (c_int, [_P, c_size_t, _P, _P]),
     "drrt_reduce_scatter_grad": (c_int, [_P, c_size_t, _I, _P, _P]),
+    "drrt_adam_step_peers": (c_int, [_P, _P, _I, _I, _P, _P, _I, _I, _I, _I, _I, _I, _F, _F, _F, _F, _F, _U, _P]),
+    "drrt_ipc_export": (c_int, [_P, _P, _P]),
+    "drrt_ipc_open": (c_int, [_P, ctypes.c_uint64, _P]),
+    "drrt_ipc_close_all": (c_int, []),
     "drrt_allgather_grid": (c_int, [_P, c_size_t, _I, _P, _P]),
 }
 

@@ -9,6 +9,8 @@
 #include <dlfcn.h>
 #include <mutex>
 #include <string>
+#include <utility>
+#include <vector>
 
 #include "../../include/drrt_b200.h"
 #include "drrt_launch.h"
@@ -242,6 +244,76 @@ int drrt_allreduce_grad(float *grad, size_t count, void *comm, drrt_stream_t str
   if (!nccl_load()) { set_err("libnccl.so.2 not found"); return DRRT_ERR_NCCL; }
   int rc = g_nccl.allreduce(grad, grad, count, 7, 0, comm, (cudaStream_t) stream);
   if (rc) return nccl_fail("ncclAllReduce", rc);
+  return DRRT_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Peer mappings for drrt_adam_step_peers: CUDA IPC handles of the allocations that hold each rank's grid and
+// gradient.  The caller's buffers usually sit inside a larger allocation (a caching allocator's segment), so the
+// handle is taken for the allocation's base (cuMemGetAddressRange) and travels with the offset; an allocation is
+// opened once per process however many buffers live in it.
+// ---------------------------------------------------------------------------
+typedef int (*fn_addr_range_t)(unsigned long long *, size_t *, unsigned long long);
+static fn_addr_range_t cu_addr_range() {
+  static fn_addr_range_t f = [] {
+    void *h = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL);
+    return h ? (fn_addr_range_t) dlsym(h, "cuMemGetAddressRange_v2") : (fn_addr_range_t) nullptr;
+  }();
+  return f;
+}
+
+static std::mutex g_ipc_mu;
+static std::vector<std::pair<cudaIpcMemHandle_t, void *>> g_ipc_open;
+
+int drrt_ipc_export(const void *ptr, char handle[DRRT_IPC_HANDLE_BYTES], uint64_t *offset) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == DRRT_IPC_HANDLE_BYTES, "IPC handle size");
+  if (!ptr || !handle || !offset) { set_err("ipc_export: NULL argument"); return DRRT_ERR_INVALID_ARGUMENT; }
+  fn_addr_range_t range = cu_addr_range();
+  if (!range) { set_err("libcuda.so.1: cuMemGetAddressRange not found"); return DRRT_ERR_CUDA; }
+  unsigned long long base = 0;
+  size_t size = 0;
+  if (range(&base, &size, (unsigned long long) (uintptr_t) ptr) != 0) {
+    set_err("ipc_export: not a device allocation"); return DRRT_ERR_CUDA;
+  }
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, (void *) (uintptr_t) base);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    set_err(std::string("cudaIpcGetMemHandle: ") + cudaGetErrorString(e) +
+            " (the buffer must come from cudaMalloc, not from a virtual-memory / async pool)");
+    return DRRT_ERR_CUDA;
+  }
+  memcpy(handle, &h, sizeof h);
+  *offset = (uint64_t) ((uintptr_t) ptr - (uintptr_t) base);
+  return DRRT_OK;
+}
+
+int drrt_ipc_open(const char handle[DRRT_IPC_HANDLE_BYTES], uint64_t offset, void **ptr) {
+  if (!handle || !ptr) { set_err("ipc_open: NULL argument"); return DRRT_ERR_INVALID_ARGUMENT; }
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof h);
+  std::lock_guard<std::mutex> lk(g_ipc_mu);
+  void *base = nullptr;
+  for (auto &o : g_ipc_open)
+    if (memcmp(&o.first, &h, sizeof h) == 0) base = o.second;
+  if (!base) {
+    cudaError_t e = cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      set_err(std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(e));
+      return DRRT_ERR_CUDA;
+    }
+    g_ipc_open.emplace_back(h, base);
+  }
+  *ptr = (char *) base + offset;
+  return DRRT_OK;
+}
+
+int drrt_ipc_close_all(void) {
+  std::lock_guard<std::mutex> lk(g_ipc_mu);
+  for (auto &o : g_ipc_open) cudaIpcCloseMemHandle(o.second);
+  g_ipc_open.clear();
+  cudaGetLastError();
   return DRRT_OK;
 }
 

@@ -153,6 +153,12 @@ int launch_adam_step(float *n, const float *grad, float *m, float *v, int S0, in
                      int i0_count, int step,
                      float lr, float beta1, float beta2, float eps, float clamp_min, bool zero_boundary,
                      bool clamp, cudaStream_t s);
+// sharded step over peer memory: host arrays of `nranks` device pointers to every rank's full grid / gradient
+constexpr int kMaxPeers = 16;
+int launch_adam_step_peers(float *const *n_replicas, const float *const *grad_replicas, int nranks, int self,
+                           float *m, float *v, int S0, int S1, int S2, int i0_begin, int i0_count, int step,
+                           float lr, float beta1, float beta2, float eps, float clamp_min, bool zero_boundary,
+                           bool clamp, cudaStream_t s);
 int launch_upres_volume(const float *src, int s0, int s1, int s2, float *dst, int d0, int d1, int d2,
                         cudaStream_t s);
 

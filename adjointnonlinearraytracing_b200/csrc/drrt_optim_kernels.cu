@@ -84,6 +84,93 @@ int launch_adam_step(float *n, const float *grad, float *m, float *v, int S0, in
 }
 
 // ---------------------------------------------------------------------------
+// Sharded optimiser step over peer memory: ONE kernel in place of
+// reduce-scatter + slab Adam + all-gather.  Every rank owns the planes [i0_begin, i0_begin + count)
+// of the grid; for each voxel of its slab it loads the P private gradients straight from the
+// peers' grids over NVLink (P2P loads, summed in rank order, so the result does not depend on
+// which rank owns the slab), applies boundary-zero + Adam + clamp with its slab of the Adam
+// state, and stores the new value into all P replicas of the grid (P2P stores).  The caller
+// brackets the launch with two stream-ordered barriers (dist.PeerShardedAdam).
+// ---------------------------------------------------------------------------
+struct PeerPtrs {
+  float *n[kMaxPeers];
+  const float *g[kMaxPeers];
+  int P;
+};
+
+template <int VEC>
+__global__ void __launch_bounds__(128) adam_step_peers_kernel(PeerPtrs pp, float *__restrict__ m, float *__restrict__ v,
+                                                              int S0, int S1, int S2, int i0_begin, int bpr, AdamP p) {
+  const int row = blockIdx.x / bpr;  // (i0 - i0_begin) * S1 + i1
+  const int i0 = row / S1 + i0_begin, i1 = row - (row / S1) * S1;
+  const int i2 = ((blockIdx.x - row * bpr) * blockDim.x + threadIdx.x) * VEC;
+  if (i2 >= S2) return;
+  const bool row_boundary = p.zero_boundary && (i0 == 0 || i0 == S0 - 1 || i1 == 0 || i1 == S1 - 1);
+  const size_t local = (size_t) row * S2 + i2;                    // within the slab (Adam state)
+  const size_t base = ((size_t) i0 * S1 + i1) * S2 + i2;          // within the whole grid (replicas)
+  if (VEC == 4) {
+    // all peer loads are issued before the first add (NVLink latency is ~2 us: keep them in flight together)
+    float4 t[kMaxPeers];
+#pragma unroll
+    for (int r = 0; r < kMaxPeers; ++r)
+      if (r < pp.P) t[r] = __ldcs(reinterpret_cast<const float4 *>(pp.g[r] + base));
+    float4 gg = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int r = 0; r < kMaxPeers; ++r)
+      if (r < pp.P) { gg.x += t[r].x; gg.y += t[r].y; gg.z += t[r].z; gg.w += t[r].w; }
+    float4 nn = *reinterpret_cast<const float4 *>(pp.n[0] + base);  // replicas are identical: any copy will do
+    float4 mm = *reinterpret_cast<float4 *>(m + local), vv = *reinterpret_cast<float4 *>(v + local);
+    if (row_boundary) gg = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.zero_boundary && i2 == 0) gg.x = 0.f;
+    if (p.zero_boundary && i2 + 3 == S2 - 1) gg.w = 0.f;
+    adam_one(nn.x, gg.x, mm.x, vv.x, p); adam_one(nn.y, gg.y, mm.y, vv.y, p);
+    adam_one(nn.z, gg.z, mm.z, vv.z, p); adam_one(nn.w, gg.w, mm.w, vv.w, p);
+    for (int r = 0; r < pp.P; ++r) *reinterpret_cast<float4 *>(pp.n[r] + base) = nn;
+    *reinterpret_cast<float4 *>(m + local) = mm;
+    *reinterpret_cast<float4 *>(v + local) = vv;
+  } else {
+    float gg = 0.f;
+    for (int r = 0; r < pp.P; ++r) gg += pp.g[r][base];
+    float nn = pp.n[0][base], mm = m[local], vv = v[local];
+    if (row_boundary || (p.zero_boundary && (i2 == 0 || i2 == S2 - 1))) gg = 0.f;
+    adam_one(nn, gg, mm, vv, p);
+    for (int r = 0; r < pp.P; ++r) pp.n[r][base] = nn;
+    m[local] = mm; v[local] = vv;
+  }
+}
+
+int launch_adam_step_peers(float *const *n_replicas, const float *const *grad_replicas, int nranks, int self,
+                           float *m, float *v, int S0, int S1, int S2, int i0_begin, int i0_count, int step,
+                           float lr, float beta1, float beta2, float eps, float clamp_min, bool zero_boundary,
+                           bool clamp, cudaStream_t s) {
+  if ((int64_t) i0_count * S1 * S2 <= 0) return 0;
+  if (nranks < 1 || nranks > kMaxPeers || self < 0 || self >= nranks) return -2;
+  PeerPtrs pp;
+  pp.P = nranks;
+  uintptr_t bits = (uintptr_t) m | (uintptr_t) v;
+  for (int r = 0; r < nranks; ++r) {
+    pp.n[r] = n_replicas[r]; pp.g[r] = grad_replicas[r];
+    if (!pp.n[r] || !pp.g[r]) return -2;
+    bits |= (uintptr_t) pp.n[r] | (uintptr_t) pp.g[r];
+  }
+  // read this rank's own copy of n (local HBM) rather than a peer's
+  float *t = pp.n[0]; pp.n[0] = pp.n[self]; pp.n[self] = t;
+  AdamP p;
+  const double bc1 = 1.0 - pow((double) beta1, (double) step), bc2 = 1.0 - pow((double) beta2, (double) step);
+  p.lr_over_bc1 = (float) ((double) lr / bc1);
+  p.rsqrt_bc2 = (float) (1.0 / sqrt(bc2));
+  p.beta1 = beta1; p.beta2 = beta2; p.eps = eps; p.clamp_min = clamp_min;
+  p.zero_boundary = zero_boundary; p.clamp = clamp;
+  const bool vec = (S2 % 4 == 0) && ((bits & 15) == 0);
+  const int bpr = (S2 / (vec ? 4 : 1) + 127) / 128;
+  const int64_t nblocks = (int64_t) i0_count * S1 * bpr;
+  if (nblocks > 0x7fffffffLL) return -1;
+  if (vec) adam_step_peers_kernel<4><<<(unsigned) nblocks, 128, 0, s>>>(pp, m, v, S0, S1, S2, i0_begin, bpr, p);
+  else adam_step_peers_kernel<1><<<(unsigned) nblocks, 128, 0, s>>>(pp, m, v, S0, S1, S2, i0_begin, bpr, p);
+  return 1;
+}
+
+// ---------------------------------------------------------------------------
 // upres_volume (core/grid.py:318-330 -> Grid.GetLinear :227-273), evaluated like the
 // reference in float64 (core/optimizer.py:10 converts to double first):
 //   x_k = linspace(0, 1, d_k)[i_k];  norm = x / h, h = 1 / max(s_0 - 1, 1);

@@ -150,6 +150,97 @@ class ShardedAdam:
         return n
 
 
+class PeerShardedAdam:
+    """``ShardedAdam`` as ONE kernel over peer memory (NVLink P2P) instead of three passes: for every voxel of this
+    rank's slab ``drrt_adam_step_peers`` loads the ``world`` private gradients straight from the peers' grids, applies
+    boundary-zero + Adam + clamp and stores the new value into all ``world`` replicas of ``n``.
+
+    ``n`` and ``grad`` are this rank's replica of the grid and its private gradient buffer; both must stay the same
+    buffers for the lifetime of the object (the peers map them through CUDA IPC once, here) and must come from
+    ``cudaMalloc`` (PyTorch's default allocator; not expandable segments / cudaMallocAsync).  ``step()`` is ordered
+    after every rank's adjoint and before every rank's next read of ``n`` by two stream-ordered barriers (a 4-byte
+    NCCL all-reduce each), so nothing synchronises with the host.  Single node only.
+    """
+
+    def __init__(self, n: torch.Tensor, grad: torch.Tensor, lr: float, betas=(0.9, 0.999), eps: float = 1e-8,
+                 clamp_min: float = 1.0, allreduce: Optional[GradAllReduce] = None):
+        for name, t in (("n", n), ("grad", grad)):
+            if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.dim() == 3):
+                raise RuntimeError(f"{name}: expected a contiguous float32 3-D CUDA tensor")
+        if grad.shape != n.shape:
+            raise RuntimeError("Resolution doesn't match data")
+        self.ar = allreduce if allreduce is not None else GradAllReduce()
+        self.world, self.rank = self.ar.world, self.ar.rank
+        if self.world > 1 and self.ar.backend != "nccl-native":
+            raise RuntimeError("PeerShardedAdam needs the NCCL communicator of GradAllReduce (GPU ranks of one node)")
+        if self.world > _capi.DRRT_MAX_PEERS:
+            raise RuntimeError(f"PeerShardedAdam: at most {_capi.DRRT_MAX_PEERS} ranks")
+        if n.shape[0] % self.world:
+            raise RuntimeError(f"PeerShardedAdam: {n.shape[0]} planes do not split into {self.world} equal slabs")
+        self.n, self.grad = n, grad
+        self.planes = n.shape[0] // self.world
+        self.i0 = self.rank * self.planes
+        self.lr, self.betas, self.eps, self.clamp_min = float(lr), tuple(betas), float(eps), float(clamp_min)
+        self.step_count = 0
+        slab_shape = (self.planes,) + tuple(n.shape[1:])
+        self.exp_avg = torch.zeros(slab_shape, device=n.device)
+        self.exp_avg_sq = torch.zeros(slab_shape, device=n.device)
+        self._token = torch.zeros(1, device=n.device)
+        lib = _capi.load()
+        mine = []
+        with torch.cuda.device(n.device):
+            for t in (n, grad):
+                h = ctypes.create_string_buffer(_capi.DRRT_IPC_HANDLE_BYTES)
+                off = ctypes.c_uint64(0)
+                _capi.check(lib.drrt_ipc_export(c_void_p(t.data_ptr()), h, ctypes.byref(off)))
+                mine.append((bytes(h.raw), int(off.value)))
+            everyone = [None] * self.world
+            if self.world > 1:
+                dist.all_gather_object(everyone, mine, group=self.ar.group)
+            else:
+                everyone[0] = mine
+            ptrs = [[0] * self.world, [0] * self.world]
+            for r in range(self.world):
+                for k in range(2):
+                    if r == self.rank:
+                        ptrs[k][r] = (n, grad)[k].data_ptr()
+                    else:
+                        hb, off = everyone[r][k]
+                        out = c_void_p()
+                        _capi.check(lib.drrt_ipc_open(ctypes.create_string_buffer(hb, _capi.DRRT_IPC_HANDLE_BYTES), off,
+                                                      ctypes.byref(out)))
+                        ptrs[k][r] = out.value
+        self._n_ptrs = (c_void_p * self.world)(*ptrs[0])
+        self._g_ptrs = (c_void_p * self.world)(*ptrs[1])
+        if self.world > 1:
+            dist.barrier(group=self.ar.group)  # every peer has mapped every buffer
+
+    def _barrier(self):
+        if self.world > 1:
+            self.ar(self._token)
+
+    def step(self) -> torch.Tensor:
+        """Uses the gradient every rank has accumulated in its ``grad`` buffer.  Returns ``n`` (updated everywhere)."""
+        n = self.n
+        self._barrier()  # every rank's adjoint has finished writing its gradient grid
+        self.step_count += 1
+        with torch.cuda.device(n.device):
+            stream = c_void_p(torch.cuda.current_stream(n.device).cuda_stream)
+            _capi.check(_capi.load().drrt_adam_step_peers(
+                self._n_ptrs, self._g_ptrs, self.world, self.rank, c_void_p(self.exp_avg.data_ptr()),
+                c_void_p(self.exp_avg_sq.data_ptr()), int(n.shape[0]), int(n.shape[1]), int(n.shape[2]), self.i0,
+                self.planes, self.step_count, self.lr, self.betas[0], self.betas[1], self.eps, self.clamp_min, 0, stream))
+        self._barrier()  # every rank's slab has landed in every replica
+        return n
+
+    def close(self):
+        """Unmap the peers' buffers (all PeerShardedAdam objects of this process)."""
+        if self.world > 1:
+            torch.cuda.synchronize(self.n.device)
+            dist.barrier(group=self.ar.group)
+            _capi.load().drrt_ipc_close_all()
+
+
 class ShardedTracer:
     """Forward + adjoint over this rank's ray block with the all-reduced gradient.
 

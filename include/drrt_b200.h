@@ -231,6 +231,16 @@ int drrt_adam_step(float *n, const float *grad, float *exp_avg, float *exp_avg_s
 int drrt_adam_step_slab(float *n, const float *grad, float *exp_avg, float *exp_avg_sq, int S0, int S1, int S2,
                         int i0_begin, int i0_count, int step, float lr, float beta1, float beta2, float eps,
                         float clamp_min, unsigned flags, drrt_stream_t stream);
+/* The sharded step as ONE kernel over peer memory (NVLink P2P) instead of reduce-scatter + slab step + all-gather:
+ * `n_replicas` / `grad_replicas` are HOST arrays of `nranks` device pointers to every rank's full grid and full
+ * private gradient grid (peer mappings of the other ranks' buffers, e.g. CUDA IPC).  For each voxel of this rank's
+ * slab the kernel sums the nranks gradients in rank order, applies the step with this rank's slab of the Adam state
+ * and writes the new value into all nranks replicas.  The caller must order it after every rank's adjoint and before
+ * every rank's next read of the grid (two stream-ordered barriers; dist.PeerShardedAdam). */
+int drrt_adam_step_peers(float *const *n_replicas, const float *const *grad_replicas, int nranks, int rank,
+                         float *exp_avg_slab, float *exp_avg_sq_slab, int S0, int S1, int S2, int i0_begin,
+                         int i0_count, int step, float lr, float beta1, float beta2, float eps, float clamp_min,
+                         unsigned flags, drrt_stream_t stream);
 int drrt_upres_volume(const float *src, int s0, int s1, int s2, float *dst, int d0, int d1, int d2,
                       drrt_stream_t stream);
 
@@ -346,6 +356,14 @@ int drrt_allreduce_grad(float *grad, size_t count, void *comm, drrt_stream_t str
  *   drrt_adam_step_slab       on that slab (above), then
  *   drrt_allgather_grid:      in place; every rank contributes grid[rank * slab_count, ...) and receives the rest. */
 int drrt_reduce_scatter_grad(float *grad, size_t slab_count, int rank, void *comm, drrt_stream_t stream);
+/* Peer mappings for drrt_adam_step_peers (CUDA IPC).  drrt_ipc_export: handle of the device allocation that holds
+ * `ptr` and ptr's offset inside it (the buffer must come from cudaMalloc).  drrt_ipc_open, in another process on the
+ * same node: the address `ptr` has there, usable by kernels of the calling thread's current device (peer access is
+ * enabled by the driver); an allocation is opened once per process.  drrt_ipc_close_all unmaps everything. */
+#define DRRT_IPC_HANDLE_BYTES 64
+int drrt_ipc_export(const void *ptr, char handle[DRRT_IPC_HANDLE_BYTES], uint64_t *offset);
+int drrt_ipc_open(const char handle[DRRT_IPC_HANDLE_BYTES], uint64_t offset, void **ptr);
+int drrt_ipc_close_all(void);
 int drrt_allgather_grid(float *grid, size_t slab_count, int rank, void *comm, drrt_stream_t stream);
 
 #ifdef __cplusplus

@@ -194,3 +194,60 @@ def test_sharded_adam_two_gpus_nccl(cuda_lib, tmp_path):
     for r in range(2):
         err, merr = np.load(tmp_path / f"err{r}.npy")
         assert err <= 1e-6 and merr <= 1e-6, (r, err, merr)
+
+
+def _peer_adam_worker(rank, world, port, out_dir):
+    import os, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from adjointnonlinearraytracing_b200 import ops
+        from adjointnonlinearraytracing_b200.dist import GradAllReduce, PeerShardedAdam
+        ar = GradAllReduce()
+        errs = []
+        for shape in ((32, 20, 24), (6, 7, 5)):  # float4 rows / odd rows (scalar kernel)
+            gen = torch.Generator(device="cuda").manual_seed(7)  # the same stream of numbers on every rank
+            n0 = 1.0 + 0.2 * torch.rand(shape, device="cuda", generator=gen)
+            grads = [[torch.randn(shape, device="cuda", generator=gen) for _ in range(world)] for _ in range(3)]
+            n = n0.clone(); gbuf = torch.zeros_like(n)
+            opt = PeerShardedAdam(n, gbuf, 1e-2, allreduce=ar)
+            ref = n0.clone(); m = torch.zeros_like(ref); v = torch.zeros_like(ref)
+            for it in range(3):
+                gbuf.copy_(grads[it][rank])           # stands for the adjoint writing this rank's gradient
+                opt.step()
+                total = grads[it][0].clone()
+                for r in range(1, world):
+                    total += grads[it][r]             # rank order, like the kernel
+                ops.adam_step_(ref, total, m, v, it + 1, 1e-2)
+            torch.cuda.synchronize()
+            lo, hi = opt.i0, opt.i0 + opt.planes
+            errs += [float((n - ref).abs().max()), float((opt.exp_avg - m[lo:hi]).abs().max()),
+                     float(torch.equal(n, ref))]
+            np.save(os.path.join(out_dir, f"pn{rank}_{shape[0]}.npy"), n.cpu().numpy())
+        np.save(os.path.join(out_dir, f"perr{rank}.npy"), np.array(errs))
+        opt.close()
+        ar.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_peer_sharded_adam_two_gpus(cuda_lib, tmp_path):
+    """The one-kernel sharded step over peer memory (CUDA IPC + NVLink loads / stores) against the whole-grid
+    step on the rank-ordered sum: bit-identical, and every replica ends up the same (needs 2 GPUs)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import socket
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+    mp.spawn(_peer_adam_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    for k in (32, 6):
+        assert np.array_equal(np.load(tmp_path / f"pn0_{k}.npy"), np.load(tmp_path / f"pn1_{k}.npy"))
+    for r in range(2):
+        e = np.load(tmp_path / f"perr{r}.npy")
+        assert e[0] == 0 and e[1] == 0 and e[2] == 1 and e[3] == 0 and e[4] == 0 and e[5] == 1, (r, e)

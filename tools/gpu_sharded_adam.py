@@ -15,7 +15,7 @@ import __graft_entry__ as ge
 
 ge.build()
 from adjointnonlinearraytracing_b200 import ops  # noqa: E402
-from adjointnonlinearraytracing_b200.dist import GradAllReduce, ShardedAdam  # noqa: E402
+from adjointnonlinearraytracing_b200.dist import GradAllReduce, PeerShardedAdam, ShardedAdam  # noqa: E402
 
 rank = int(os.environ.get("LOCAL_RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1))
 torch.cuda.set_device(rank)
@@ -56,6 +56,15 @@ del m, v
 n2 = n.clone()
 opt = ShardedAdam(n2, 1e-3, allreduce=ar)
 t_sh = timeit(lambda: opt.step(grad))
+del opt
+n3 = n.clone()
+popt = PeerShardedAdam(n3, grad, 1e-3, allreduce=ar)
+t_peer = timeit(lambda: popt.step())
+t_bar = timeit(lambda: popt._barrier())
+if rank == 0:
+    print(f"{res}^3, {world} ranks: one kernel over peer memory (two 4-byte barriers + P2P sum + Adam + P2P store) "
+          f"{t_peer:.3f} ms; one barrier alone {t_bar:.3f} ms", flush=True)
+popt.close()
 if rank == 0:
     print(f"{res}^3, {world} ranks: all-reduce alone {t_ar:.3f} ms; all-reduce + whole-grid Adam {t_full:.3f} ms; "
           f"reduce-scatter + slab Adam + all-gather {t_sh:.3f} ms; Adam state per rank {2 * n.numel() * 4 / 2**20:.0f} -> "
