@@ -56,6 +56,7 @@ del m, v
 n2 = n.clone()
 opt = ShardedAdam(n2, 1e-3, allreduce=ar)
 t_sh = timeit(lambda: opt.step(grad))
+state_mib = 2 * opt.exp_avg.numel() * 4 / 2**20
 del opt
 n3 = n.clone()
 popt = PeerShardedAdam(n3, grad, 1e-3, allreduce=ar)
@@ -68,7 +69,7 @@ popt.close()
 if rank == 0:
     print(f"{res}^3, {world} ranks: all-reduce alone {t_ar:.3f} ms; all-reduce + whole-grid Adam {t_full:.3f} ms; "
           f"reduce-scatter + slab Adam + all-gather {t_sh:.3f} ms; Adam state per rank {2 * n.numel() * 4 / 2**20:.0f} -> "
-          f"{2 * opt.exp_avg.numel() * 4 / 2**20:.0f} MiB", flush=True)
+          f"{state_mib:.0f} MiB", flush=True)
 ar.close()
 if world > 1:
     dist.destroy_process_group()
