@@ -250,7 +250,10 @@ class ShardedTracer:
     """
 
     def __init__(self, rif: torch.Tensor, h: float, ds: float, flags: int = 0,
-                 allreduce: Optional[GradAllReduce] = None):
+                 allreduce: Optional[GradAllReduce] = None, reduce: bool = True):
+        # reduce=False: ``backtrace`` leaves this rank's PRIVATE gradient in ``self.grad`` -- the input of
+        # ``PeerShardedAdam(rif, st.grad, lr)`` / ``ShardedAdam.step(st.grad)``, which do the sum themselves
+        self.reduce = bool(reduce)
         self.rif, self.h, self.ds, self.flags = rif, float(h), float(ds), int(flags)
         self.allreduce = allreduce if allreduce is not None else GradAllReduce()
         self.grad = torch.empty_like(rif)
@@ -262,4 +265,4 @@ class ShardedTracer:
     def backtrace(self, xt, vt, dx, dv):
         g = ops.backtrace(self.rif, xt, vt, dx, dv, self.h, self.ds, flags=self.flags, stats=self.stats,
                           out=self.grad)
-        return self.allreduce(g)
+        return self.allreduce(g) if self.reduce else g
