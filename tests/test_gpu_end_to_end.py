@@ -134,6 +134,7 @@ def _two_rank_loop_worker(rank, world, port, out_dir):
 
 
 @pytest.mark.gpu
+@pytest.mark.timeout(300)  # a rendezvous that never completes fails the test instead of hanging the run
 def test_two_gpu_iteration_sharded_rays_peer_optimiser(cuda_lib, tmp_path):
     """Two ranks, rays sharded: all-reduced gradient == single-batch gradient; trace -> adjoint -> optimiser step
     with the peer-memory kernel == the same loop with NCCL reduce-scatter / all-gather (needs 2 GPUs)."""

@@ -180,6 +180,7 @@ def _nccl_adam_worker(rank, world, port, out_dir):
 
 
 @pytest.mark.gpu
+@pytest.mark.timeout(300)  # a rendezvous that never completes fails the test instead of hanging the run
 def test_sharded_adam_two_gpus_nccl(cuda_lib, tmp_path):
     """reduce-scatter -> slab Adam -> all-gather over NCCL against all-reduce -> whole-grid Adam (needs 2 GPUs)."""
     if torch.cuda.device_count() < 2:
@@ -236,6 +237,7 @@ def _peer_adam_worker(rank, world, port, out_dir):
 
 
 @pytest.mark.gpu
+@pytest.mark.timeout(300)  # a rendezvous that never completes fails the test instead of hanging the run
 def test_peer_sharded_adam_two_gpus(cuda_lib, tmp_path):
     """The one-kernel sharded step over peer memory (CUDA IPC + NVLink loads / stores) against the whole-grid
     step on the rank-ordered sum: bit-identical, and every replica ends up the same (needs 2 GPUs)."""
