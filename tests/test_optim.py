@@ -253,3 +253,26 @@ def test_peer_sharded_adam_two_gpus(cuda_lib, tmp_path):
     for r in range(2):
         e = np.load(tmp_path / f"perr{r}.npy")
         assert e[0] == 0 and e[1] == 0 and e[2] == 1 and e[3] == 0 and e[4] == 0 and e[5] == 1, (r, e)
+
+
+@pytest.mark.gpu
+def test_peer_sharded_adam_single_rank_equals_whole_grid(cuda_lib):
+    """world = 1: the peer-memory kernel with one replica is the whole-grid step, bit for bit (float4 and scalar
+    rows), through the same export / pointer-table path the multi-GPU case uses."""
+    from adjointnonlinearraytracing_b200 import ops
+    from adjointnonlinearraytracing_b200.dist import PeerShardedAdam
+    gen = torch.Generator(device="cuda").manual_seed(21)
+    for shape in ((12, 8, 16), (5, 6, 7)):
+        n0 = 1.0 + 0.2 * torch.rand(shape, device="cuda", generator=gen)
+        n = n0.clone(); gbuf = torch.zeros_like(n)
+        opt = PeerShardedAdam(n, gbuf, 1e-2)
+        assert opt.world == 1 and opt.planes == shape[0]
+        ref = n0.clone(); m = torch.zeros_like(ref); v = torch.zeros_like(ref)
+        for it in range(3):
+            g = torch.randn(shape, device="cuda", generator=gen)
+            gbuf.copy_(g)
+            opt.step()
+            ops.adam_step_(ref, g, m, v, it + 1, 1e-2)
+        assert torch.equal(n, ref) and torch.equal(opt.exp_avg, m) and torch.equal(opt.exp_avg_sq, v)
+    with pytest.raises(RuntimeError):
+        PeerShardedAdam(n, torch.zeros(5, 6, 8, device="cuda"), 1e-2)
