@@ -189,7 +189,7 @@ class PeerShardedAdam:
         lib = _capi.load()
         mine = []
         with torch.cuda.device(n.device):
-            for t in (n, grad):
+            for t in ((n, grad) if self.world > 1 else ()):  # one rank: nothing to map, any allocator will do
                 h = ctypes.create_string_buffer(_capi.DRRT_IPC_HANDLE_BYTES)
                 off = ctypes.c_uint64(0)
                 _capi.check(lib.drrt_ipc_export(c_void_p(t.data_ptr()), h, ctypes.byref(off)))

@@ -258,7 +258,7 @@ def test_peer_sharded_adam_two_gpus(cuda_lib, tmp_path):
 @pytest.mark.gpu
 def test_peer_sharded_adam_single_rank_equals_whole_grid(cuda_lib):
     """world = 1: the peer-memory kernel with one replica is the whole-grid step, bit for bit (float4 and scalar
-    rows), through the same export / pointer-table path the multi-GPU case uses."""
+    rows), through the same pointer-table path the multi-GPU case uses."""
     from adjointnonlinearraytracing_b200 import ops
     from adjointnonlinearraytracing_b200.dist import PeerShardedAdam
     gen = torch.Generator(device="cuda").manual_seed(21)
