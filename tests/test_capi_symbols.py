@@ -77,6 +77,20 @@ def test_argument_validation_of_the_epilogue_entry_points(cuda_lib):
     assert lib.drrt_backtrace_rays(buf, null, 4, 4, 1, buf, buf, buf, buf, null, 8, 3, 0.25, 0.0, buf, buf, buf,
                                    null, null, 0, null) < 0
     assert lib.drrt_adam_step(buf, buf, buf, buf, 4, 4, 4, 0, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, null) == -1
+    # sharded optimiser step: slabs must lie inside the grid, an empty slab is a no-op, 1..16 ranks
+    assert lib.drrt_adam_step_slab(buf, buf, buf, buf, 4, 4, 4, 3, 2, 1, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, null) == -2
+    assert "slab" in err()
+    assert lib.drrt_adam_step_slab(buf, buf, buf, buf, 4, 4, 4, -1, 2, 1, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, null) == -2
+    assert lib.drrt_adam_step_slab(null, null, null, null, 4, 4, 4, 2, 0, 1, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, null) == 0
+    assert lib.drrt_adam_step_slab(buf, null, buf, buf, 4, 4, 4, 0, 2, 1, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, null) == -1
+    tbl = (ctypes.c_void_p * 17)(*([ctypes.addressof(buf)] * 17))
+    assert lib.drrt_adam_step_peers(tbl, tbl, 17, 0, buf, buf, 4, 4, 4, 0, 4, 1, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, null) == -1
+    assert "ranks" in err()
+    assert lib.drrt_adam_step_peers(tbl, tbl, 2, 2, buf, buf, 4, 4, 4, 0, 2, 1, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, null) == -1
+    assert lib.drrt_adam_step_peers(null, tbl, 2, 0, buf, buf, 4, 4, 4, 0, 2, 1, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, null) == -1
+    assert lib.drrt_adam_step_peers(tbl, tbl, 2, 0, buf, buf, 4, 4, 4, 2, 3, 1, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, null) == -2
+    assert lib.drrt_ipc_export(null, buf, buf) == -1 and lib.drrt_ipc_open(null, 0, buf) == -1
+    assert lib.drrt_ipc_close_all() == 0
 
 
 def test_scratch_bytes_contract(cuda_lib):
