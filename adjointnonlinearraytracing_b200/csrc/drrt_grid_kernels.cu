@@ -719,9 +719,15 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : 
   sg.data = a.sdf;
   bool outside = false;
   f3 xl = {0, 0, 0}, vl = {0, 0, 0};  // RG: (x_k, v_k) of the last sample that updated lambda/mu
+  // RG: a ray launched INSIDE the region the adjoint integrates through (trace_sdf's rays start inside the
+  // object, src/tracer.cpp:271-277) is re-integrated past its launch point; the backward samples retrace the
+  // forward ones, so the sample within half a step of pos0 is x_0 and (lambda, mu) after it are dL/dx_0, dL/dv_0.
+  f3 p0 = {0, 0, 0}, lcap = {0, 0, 0}, mcap = {0, 0, 0};
+  bool got = false;
   if (valid) {
     x = ld3(a.xt, r, a.N, a.layout); v = ld3(a.vt, r, a.N, a.layout);
     xl = x; vl = v;
+    if (RG && a.pos0) p0 = ld3(a.pos0, r, a.N, a.layout);
     la = ld3(a.dx, r, a.N, a.layout); mu = ld3(a.dv, r, a.N, a.layout);
     mu.x = add_(mu.x, mul_(ds, la.x)); mu.y = add_(mu.y, mul_(ds, la.y)); mu.z = add_(mu.z, mul_(ds, la.z));  // :410
     f3 nv = {-v.x, -v.y, -v.z};
@@ -821,7 +827,15 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : 
           la.z = fmaf(ds, fmaf(dn, nx.z, h2), la.z);
           mu.x = fmaf(ds, la.x, mu.x); mu.y = fmaf(ds, la.y, mu.y); mu.z = fmaf(ds, la.z, mu.z);
         }
-        if (RG) { xl = x; vl = v; }
+        if (RG) {
+          xl = x; vl = v;
+          if (a.pos0 && !got) {
+            const float ex = x.x - p0.x, ey = x.y - p0.y, ez = x.z - p0.z;
+            if (ex * ex + ey * ey + ez * ez <= 0.25f * ds * ds * (v.x * v.x + v.y * v.y + v.z * v.z)) {
+              got = true; lcap = la; mcap = mu;
+            }
+          }
+        }
       }
     }
   }
@@ -840,12 +854,13 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : 
   if (RG && valid) {
     float k = 0.f;
     if (a.pos0) {
-      const f3 x0 = ld3(a.pos0, r, a.N, a.layout);
+      const f3 x0 = p0;
       const float num = (xl.x - x0.x) * vl.x + (xl.y - x0.y) * vl.y + (xl.z - x0.z) * vl.z;
       const float den = ds * (vl.x * vl.x + vl.y * vl.y + vl.z * vl.z);
       k = den > 0.f ? rintf(num / den) : 0.f;
     }
-    const float t = (k - 1.f) * ds;
+    float t = (k - 1.f) * ds;
+    if (got) { la = lcap; mu = mcap; t = -ds; }
     st3(a.dpos, r, a.N, a.layout, la);
     f3 dv0 = {fmaf(t, la.x, mu.x), fmaf(t, la.y, mu.y), fmaf(t, la.z, mu.z)};
     st3(a.dvel, r, a.N, a.layout, dv0);

@@ -10,6 +10,11 @@ Three checkers, all taking and returning host numpy arrays (ray vectors AoS
             ``/root/reference`` by ``oracle/build_ref.sh`` (``oracle/_ref/``);
             ``None`` if that library has not been built.
 
+``refad``   the reference's own CPU TAPE-AUTODIFF tracer ``Tracer<true,false>`` on enoki's
+            ``DiffArray`` (``oracle/ref_ad_shim.cpp``, ``oracle/_ref/libdrrt_refad_v3.so``):
+            what the reference's ``ADTracerC`` / ``ADSDFTracerC`` backward returns
+            (``core/tracer.py:45-66``); ``None`` if not built.
+
 Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline /
 ``--impl reference`` legs may import this package.  The product package
 ``adjointnonlinearraytracing_b200`` never does.
@@ -251,10 +256,45 @@ def _load_ref():
     return None
 
 
+class _RefAD:
+    """ctypes wrapper of oracle/ref_ad_shim.cpp (reference Tracer<true,false> + enoki tape)."""
+
+    def __init__(self, path):
+        self.path = path
+        self.lib = ctypes.CDLL(path)
+        self.lib.refad_trace_backward.restype = c_int
+        self.lib.refad_last_error.restype = c_char_p
+
+    def trace_backward(self, rif, pos, vel, h, ds, seed_x, seed_v, sdf=None):
+        """(xt, vt, d_rif, d_pos, d_vel) of ADTracerC (sdf=None) / ADSDFTracerC forward + backward."""
+        rif = _f32(rif); pos = _f32(pos); vel = _f32(vel); sx = _f32(seed_x); sv = _f32(seed_v)
+        W, H, D = (int(r) for r in rif.shape)
+        N = pos.shape[0]
+        P = lambda a: a.ctypes.data_as(POINTER(c_float))
+        sd = _f32(sdf) if sdf is not None else None
+        xt = np.empty_like(pos); vt = np.empty_like(pos)
+        dr = np.empty(rif.size, dtype=np.float32); dp = np.empty_like(pos); dv = np.empty_like(pos)
+        rc = self.lib.refad_trace_backward(P(rif), P(sd) if sd is not None else POINTER(c_float)(), W, H, D,
+                                           P(pos), P(vel), _i64(N), c_float(h), c_float(ds), P(sx), P(sv),
+                                           P(xt), P(vt), P(dr), P(dp), P(dv))
+        if rc != 0:
+            raise RuntimeError(self.lib.refad_last_error().decode())
+        return xt, vt, dr.reshape(rif.shape), dp, dv
+
+
+def _load_refad():
+    path = os.path.join(_HERE, "_ref", "libdrrt_refad_v3.so")
+    return _RefAD(path) if os.path.exists(path) else None
+
+
 _cache = {}
 
 
 def __getattr__(name):
+    if name == "refad":
+        if name not in _cache:
+            _cache[name] = _load_refad()
+        return _cache[name]
     if name in ("port", "port64", "ref"):
         if name not in _cache:
             if name == "port":

@@ -26,5 +26,14 @@ for v in v3 v4; do
     g++ $CXXFLAGS -march=x86-64-$v "$HERE/ref_shim.cpp" -o "$OUT/libdrrt_ref_$v.so" &
   fi
 done
+# The reference's CPU TAPE-AUTODIFF tracer, Tracer<true,false> (src/tracer.cpp:569), with enoki's
+# autodiff back end compiled from where it lies (ext/enoki/src/autodiff/autodiff.cpp; the CPU
+# instantiations are at :1229-1230).  One portable ISA build: it pins gradients, it is never timed.
+if [ ! -f "$OUT/libdrrt_refad_v3.so" ] || [ "$HERE/ref_ad_shim.cpp" -nt "$OUT/libdrrt_refad_v3.so" ] \
+   || [ "$HERE/ref_ad_stubs.cpp" -nt "$OUT/libdrrt_refad_v3.so" ]; then
+  g++ -std=c++17 -O2 -DNDEBUG -fPIC -shared -w -I"$OUT" -I"$REF/include" -I"$REF/ext/enoki/include" \
+      -march=x86-64-v3 -DENOKI_AUTODIFF_BUILD=1 "$HERE/ref_ad_shim.cpp" "$HERE/ref_ad_stubs.cpp" \
+      "$REF/ext/enoki/src/autodiff/autodiff.cpp" -o "$OUT/libdrrt_refad_v3.so" &
+fi
 wait
 ls -la "$OUT"/*.so

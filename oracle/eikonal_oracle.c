@@ -587,7 +587,12 @@ static int64_t backtrace_grid(const real *rif, const real *sdf, int W, int H, in
   real *sterm = (real *) malloc(sizeof(real) * 16 * (size_t) (N ? N : 1));
   /* ray gradients (not in the reference's backtrace; see backtrace_rays below):
    * (x_k, v_k) of the last sample that updated lambda / mu */
-  real *xl = 0, *vl = 0;
+  real *xl = 0, *vl = 0, *cap = 0;   /* cap: (la, mu) captured at the launch sample, [6] per ray, + flag */
+  unsigned char *got = 0;
+  if (dpos && pos0) {
+    cap = (real *) malloc(sizeof(real) * 6 * (size_t) (N ? N : 1));
+    got = (unsigned char *) calloc((size_t) (N ? N : 1), 1);
+  }
   if (dpos) {
     xl = (real *) malloc(sizeof(real) * 3 * (size_t) (N ? N : 1));
     vl = (real *) malloc(sizeof(real) * 3 * (size_t) (N ? N : 1));
@@ -642,6 +647,19 @@ static int64_t backtrace_grid(const real *rif, const real *sdf, int W, int H, in
       real Hm[9] = {0, hx[0], hx[1], hx[0], 0, hx[2], hx[1], hx[2], 0};
       adj_update(la, mu, ds, dn, n, nx, Hm);                              /* :434-435 */
       if (dpos) for (int k = 0; k < 3; ++k) { xl[3 * r + k] = x[k]; vl[3 * r + k] = s.v[3 * r + k]; }
+      if (got && !got[r]) {
+        /* A ray launched INSIDE the region the adjoint integrates through (trace_sdf's rays start inside
+         * the object, src/tracer.cpp:271-277) is re-integrated past its launch point; the backward samples
+         * retrace the forward ones, so the sample that coincides with pos0 (within half a step) is x_0 and
+         * (la, mu) after it are dL/dx_0, dL/dv_0. */
+        const real *p0 = pos0 + 3 * r, *vv = s.v + 3 * r;
+        real d2 = (x[0] - p0[0]) * (x[0] - p0[0]) + (x[1] - p0[1]) * (x[1] - p0[1]) + (x[2] - p0[2]) * (x[2] - p0[2]);
+        real v2 = vv[0] * vv[0] + vv[1] * vv[1] + vv[2] * vv[2];
+        if (d2 <= (real) 0.25 * ds * ds * v2) {
+          got[r] = 1;
+          for (int k = 0; k < 3; ++k) { cap[6 * r + k] = la[k]; cap[6 * r + 3 + k] = mu[k]; }
+        }
+      }
     }
     for (int t = 0; t < 16; ++t)                                          /* src/volume.cpp:217-243 */
       for (int64_t r = 0; r < N; ++r)
@@ -657,12 +675,14 @@ static int64_t backtrace_grid(const real *rif, const real *sdf, int W, int H, in
         k = den > 0 ? (real) rint((double) (num / den)) : 0;
       }
       real t = (k - 1) * ds;
+      const real *la = s.la + 3 * r, *mu = s.mu + 3 * r;
+      if (got && got[r]) { la = cap + 6 * r; mu = cap + 6 * r + 3; t = -ds; }
       for (int c = 0; c < 3; ++c) {
-        dpos[3 * r + c] = s.la[3 * r + c];
-        dvel[3 * r + c] = s.mu[3 * r + c] + t * s.la[3 * r + c];
+        dpos[3 * r + c] = la[c];
+        dvel[3 * r + c] = mu[c] + t * la[c];
       }
     }
-    free(xl); free(vl);
+    free(xl); free(vl); free(cap); free(got);
   }
   free(sidx); free(sterm);
   adj_free(&s);
