@@ -102,3 +102,65 @@ def cable_rays(s: int, radius: float = 1.0, seed: int = 0, spread: float = 0.05)
     vel = np.array([0, 1, 0]) + spread * rng.standard_normal((n, 3))
     vel /= np.linalg.norm(vel, axis=1, keepdims=True)
     return pos.astype(np.float32), vel.astype(np.float32)
+
+
+def rays_multiview(n_views: int, s: int, spp: int, seed: int = 0):
+    """n_views collimated s x s sensors around the volume centre (rotation about y), spp jittered samples
+    per pixel, launched outside the box: the batch shape of the reference's tomography driver
+    (path_matrix/run_fuel_injection_2008.py:80-92, core/source.py:345-357)."""
+    rng = np.random.default_rng(seed)
+    u = (np.arange(s) + 0.5) / s
+    yy, xx = np.meshgrid(u, u, indexing="ij")
+    P, V = [], []
+    for k in range(n_views):
+        th = np.pi * k / n_views
+        d = np.array([np.sin(th), 0.0, np.cos(th)])
+        e1 = np.array([np.cos(th), 0.0, -np.sin(th)]); e2 = np.array([0.0, 1.0, 0.0])
+        for _ in range(spp):
+            jx = (rng.uniform(-0.5, 0.5, xx.shape)) / s; jy = (rng.uniform(-0.5, 0.5, xx.shape)) / s
+            a = (xx + jx - 0.5) * 0.7; b = (yy + jy - 0.5) * 0.7
+            p = 0.5 + a[..., None] * e1 + b[..., None] * e2 - 0.9 * d
+            P.append(p.reshape(-1, 3)); V.append(np.tile(d, (s * s, 1)))
+    return np.concatenate(P).astype(np.float32), np.concatenate(V).astype(np.float32)
+
+
+# The shapes of BASELINE.json's five configurations (SURVEY.md section 8 size table) plus the reference's own
+# measurement protocol (src/test.cpp:148-206), as synthetic seeded workloads.  Used by bench.py (`configs`
+# entries of the JSON line), tools/gpu_configs.py and the reference-parity tests.
+CONFIG_NAMES = ("luneburg32", "fiber64", "cable129", "fuel65", "caustic256", "caustic256_cone", "focal512")
+
+
+def config_case(name: str) -> dict:
+    """-> dict(kind="grid"|"cable", label, rif, h / radius / length, ds, pos, vel[, target])."""
+    def grid(label, ng, field, pos, vel, step_res=2):
+        h = grid_spacing(ng)
+        return dict(kind="grid", label=label, ng=ng, rif=field(ng), h=h, ds=np.float32(h / step_res), pos=pos, vel=vel)
+    if name == "luneburg32":
+        return grid("configs[0] Luneburg lens: 32^3 lens field, 256^2 collimated rays", 32, field_luneburg, *rays_collimated(256))
+    if name == "fiber64":
+        return grid("configs[1] fibre, grid form: 64^3, 512^2 collimated rays", 64, field_bump, *rays_collimated(512))
+    if name == "cable129":
+        res, radius, length, s = 129, 1.0, 5.0, 512
+        pos, vel = cable_rays(s, radius)
+        tgt = np.tile(np.array([radius, length, radius], np.float32), (s * s, 1))
+        return dict(kind="cable", label="configs[1] fibre, cable form: 129-sample profile, R = 1, L = 5, 512^2 rays, ds = R/res/2",
+                    rif=cable_profile(res), radius=radius, length=length, ds=np.float32(radius / res / 2), pos=pos, vel=vel,
+                    target=tgt)
+    if name == "fuel65":
+        return grid("configs[2] fuel-injection tomography: 65^3, 32 views x 64^2 x 16 spp", 65, field_bump, *rays_multiview(32, 64, 16))
+    if name == "caustic256":
+        return grid("configs[3] caustic design: 256^3, 2048^2 collimated rays", 256, field_bump, *rays_collimated(2048))
+    if name == "caustic256_cone":
+        return grid("configs[3'] caustic design, oblique batch: 256^3, 2048^2 rays, cone spread 0.15", 256, field_bump,
+                    *rays_cone(2048, spread=0.15))
+    if name == "focal512":
+        return grid("configs[4] focal stack: 512^3, 1448^2 = 2.1 M rays (one GPU's share of 16.8 M over 8)", 512, field_bump,
+                    *rays_collimated(1448))
+    raise KeyError(name)
+
+
+def subsample(n_total: int, n: int) -> np.ndarray:
+    """Indices of a strided subsample of n rays spread over the whole batch."""
+    if n >= n_total:
+        return np.arange(n_total)
+    return (np.arange(n, dtype=np.int64) * n_total) // n

@@ -71,6 +71,14 @@ class _Lib:
         self.last_steps = None
 
     # -- helpers ---------------------------------------------------------
+    def isa(self):
+        """ISA of a reference-library build ("avx512" / "avx2"): enoki's rcp(h) differs between the two."""
+        f = getattr(self.lib, self.prefix + "isa", None)
+        if f is None:
+            return "port"
+        f.restype = c_char_p
+        return f().decode()
+
     def _fn(self, name, restype=None):
         f = getattr(self.lib, self.prefix + name)
         f.restype = restype if restype is not None else (_i64 if self.returns_steps else c_int)
@@ -305,3 +313,42 @@ def __getattr__(name):
                 _cache[name] = _load_ref()
         return _cache[name]
     raise AttributeError(name)
+
+
+def run_threads(fn, n):
+    """fn(i) on n host threads (ctypes calls release the GIL) -> list of results."""
+    import threading
+    out, thr = [None] * n, []
+
+    def work(i):
+        out[i] = fn(i)
+    for i in range(n):
+        t = threading.Thread(target=work, args=(i,))
+        t.start(); thr.append(t)
+    for t in thr:
+        t.join()
+    return out
+
+
+def chunk_bounds(n, threads=None):
+    threads = max(1, min(threads or len(os.sched_getaffinity(0)), n // 256 or 1))
+    return [(n * i) // threads for i in range(threads + 1)]
+
+
+def trace_backtrace_mt(lib, rif, pos, vel, dx, dv, h, ds, threads=None):
+    """Forward trace + adjoint of `lib` (ref / port) with the rays split into contiguous chunks over host
+    threads, private gradient grids summed in float64 (the reference itself is single-threaded; for
+    trace / backtrace a ray's trajectory and gradient contributions do not depend on the rest of the batch).
+    -> (xt, vt, grad float64)."""
+    bounds = chunk_bounds(pos.shape[0], threads)
+
+    def one(i):
+        a, b = bounds[i], bounds[i + 1]
+        xt, vt = lib.trace(rif, pos[a:b], vel[a:b], h, ds)
+        return xt, vt, lib.backtrace(rif, xt, vt, dx[a:b], dv[a:b], h, ds)
+    parts = run_threads(one, len(bounds) - 1)
+    xt = np.concatenate([p[0] for p in parts]); vt = np.concatenate([p[1] for p in parts])
+    grad = np.zeros(parts[0][2].shape, dtype=np.float64)
+    for p in parts:
+        grad += p[2]
+    return xt, vt, grad
