@@ -79,6 +79,15 @@ class _Lib:
         f.restype = c_char_p
         return f().decode()
 
+    def rcp(self, h):
+        """rcp(h) as this library's volume::eval_grad computes it (reference builds; port: IEEE 1/h)."""
+        f = getattr(self.lib, self.prefix + "rcp", None)
+        if f is None:
+            return np.float32(1.0) / np.float32(h)
+        f.restype = c_float
+        f.argtypes = [c_float]
+        return np.float32(f(c_float(float(h))))
+
     def _fn(self, name, restype=None):
         f = getattr(self.lib, self.prefix + name)
         f.restype = restype if restype is not None else (_i64 if self.returns_steps else c_int)
@@ -293,6 +302,36 @@ class _RefAD:
 def _load_refad():
     path = os.path.join(_HERE, "_ref", "libdrrt_refad_v3.so")
     return _RefAD(path) if os.path.exists(path) else None
+
+
+def ref_builds():
+    """Every reference-library build that can run on this host: {"v4": _Lib, "v3": _Lib}."""
+    out = {}
+    for v in (("v4", "v3") if _cpu_has_avx512() else ("v3",)):
+        path = os.path.join(_HERE, "_ref", f"libdrrt_ref_{v}.so")
+        if os.path.exists(path):
+            try:
+                out[v] = _Lib(path, "ref_", np.float32, returns_steps=False)
+            except OSError:
+                pass
+    return out
+
+
+def ref_for_spacing(h):
+    """The reference build whose rcp(h) equals the correctly rounded 1/h (what the CUDA kernels and the
+    restatement use), or None.  The reference's AVX2 / AVX-512 / CUDA builds approximate 1/h three different
+    ways (enoki rcp + Newton, rcp14 + Newton, rcp.approx.ftz); on lattice-exact samples the last ulp of
+    p * rcp(h) selects the cell, so two builds of the SAME source differ there by 5e-3 .. 3e-2 in the gradient
+    (tests/test_ref_parity_shapes.py records it).  Against the build that shares 1/h the trajectory is
+    bit-identical."""
+    want = np.float32(1.0) / np.float32(h)
+    for v, lib in ref_builds().items():
+        try:
+            if lib.rcp(h) == want:
+                return lib
+        except AttributeError:
+            pass
+    return None
 
 
 _cache = {}

@@ -102,6 +102,16 @@ const char *ref_isa() {
 #endif
 }
 
+// The library's own rcp(h) as volume::eval_grad computes it (src/volume.cpp:128 on the size-1 array h_,
+// include/volume.h:49): enoki's packet rcp is rcp14 + one Newton step on AVX-512 and rcp + Newton on AVX2,
+// neither always equal to the correctly rounded 1/h.  Tests use it to tell which build shares the GPU's
+// 1/h for a given spacing (lattice-exact samples select their cell by the last ulp of p * rcp(h)).
+float ref_rcp(float h) {
+  FloatS_ hh(h);
+  FloatS_ r = enoki::rcp(hh);
+  return r.coeff(0);
+}
+
 int ref_trace(const float *rif, int W, int H, int D, const float *pos, const float *vel, int64_t N,
               float h, float ds, float *xt, float *vt) {
   REF_TRY

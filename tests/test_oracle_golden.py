@@ -109,15 +109,15 @@ def test_port_vs_reference_library(oracle_mod):
     dx, dv = sc.seeds_normal(pos.shape[0])
     gr = oracle_mod.ref.backtrace(rif, xr, vr, dx, dv, h, ds)
     gp = oracle_mod.port.backtrace(rif, xr, vr, dx, dv, h, ds)
-    if oracle_mod.ref.isa() == "avx512":
-        # The AVX-512 build of the reference (rcp14 + Newton = correctly rounded 1/h, hardware FMA exactly
-        # where the source says fmadd) and the restatement perform the same float32 operations in the same
-        # order, scatter-adds included: measured bit-identical, endpoints and gradient (also at 256^3,
-        # tests/test_ref_parity_shapes.py).
+    if oracle_mod.ref.rcp(h) == np.float32(1.0) / h:
+        # A reference build whose rcp(h) is the correctly rounded 1/h (the AVX-512 build at this spacing;
+        # see oracle.ref_for_spacing) and the restatement perform the same float32 operations in the same
+        # order, scatter-adds included: measured bit-identical, endpoints and gradient (also at the
+        # benchmarked shapes, tests/test_ref_parity_shapes.py).
         assert np.array_equal(xr, xp) and np.array_equal(vr, vp)
         assert rel_l2(gp, gr) <= 1e-6, rel_l2(gp, gr)
     else:
-        # The AVX2 build's rcp(h) is 1 ulp low: float32 coin flips at cell faces against ANY other build of
+        # This build's rcp(h) is 1 ulp off: float32 coin flips at cell faces against ANY other build of
         # the same source (its own AVX-512 build included, tests/golden/make_golden.py prints them):
         # almost all rays agree to 1e-5 of the span, the rest are bounded by one cell-face kick.
         assert np.mean(e <= 1e-5) >= 0.995
