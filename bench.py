@@ -2,19 +2,34 @@
 """bench.py -- fwd+adjoint ray-steps/s of the eikonal tracer on B200 (BASELINE.json metric).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--scaling strong|weak] [--workload caustic256|focal512] [--no-cpu] [--no-configs]
 
-One "step" = one forward trace + one adjoint backtrace (+ gradient all-reduce when
-N > 1) over one ray batch.  Workload (config.workload): BASELINE.json configs[3]
-"caustic design": 256^3 IOR grid (Gaussian-bump field A of SURVEY.md section 8d), 2048^2 =
-4 194 304 collimated rays per GPU, ds = h/2, adjoint seeds dx = dv = 1
-(reference src/test.cpp:142-144).  Weak scaling: every rank traces its own 4M-ray batch.
+One "step" = one forward trace + one adjoint backtrace (+ gradient all-reduce when N > 1) over one
+ray batch.  Workload (config.workload): BASELINE.json configs[3] "caustic design" AS WRITTEN: 256^3 IOR
+grid (Gaussian-bump field A of SURVEY.md section 8d), 2048^2 = 4 194 304 collimated rays IN TOTAL, ds = h/2,
+adjoint seeds dx = dv = 1 (reference src/test.cpp:142-144).  N > 1: the batch is sharded in contiguous blocks
+(dist.shard_bounds), i.e. STRONG scaling; the weak figure (4 M rays per rank) is measured too and reported
+under `secondary.weak`.  Every N > 1 run checks the all-reduced gradient against a single-GPU gradient of
+the whole batch (`grad_check`) and reports the collective's own time.
 
-Printed JSON (one line, rank 0): see the task contract; `roofline`, `cpu_baseline`,
-`e2e`, `clocks`, `gpu_launches` are included.
+At N = 1 the line also carries
+  parity        the GPU against the reference's own CPU tracer (oracle/_ref) on the SAME strided subsample of
+                the benchmarked batch that the cpu_baseline leg times -- endpoints and gradient -- plus the
+                reference's own AVX2-vs-AVX-512 disagreement on it (the noise floor of this lattice-exact
+                batch) and a backed-off batch (z0 = -0.37 ds) where no lattice excuse applies; the run FAILS
+                (exit 3, after printing) when endpoints leave 1e-5 or the gradient leaves 1e-4,
+  configs       fwd / adjoint times of all five BASELINE.json configurations + the reference's own
+                step-size sweep (src/test.cpp:148-206),
+  roofline      against the roof that actually binds the dominant kernel (instruction issue; the grids are
+                L2-resident), with the section-8d algorithmic-bytes-vs-HBM figure beside it; counts taken
+                from committed ncu captures carry the hash of the kernel sources they were captured on and
+                `stale: true` is emitted when the built sources differ.
 """
 from __future__ import annotations
 
 import argparse
+import glob
+import hashlib
 import json
 import os
 import sys
@@ -31,8 +46,12 @@ SENSOR = 2048
 METRIC = "fwd+adjoint ray-steps/sec at 256^3 grid"
 UNIT = "ray-steps/s"
 BYTES_FWD, BYTES_ADJ = 32, 64  # algorithmic bytes per ray-step, SURVEY.md section 8d
-WORKLOAD = (f"caustic-256 (BASELINE.json configs[3]): {NG}^3 bump IOR grid, {SENSOR}^2 = {SENSOR * SENSOR} "
-            "collimated rays per GPU, ds = h/2, seeds dx=dv=1")
+END_TOL, GRAD_TOL = 1e-5, 1e-4  # north-star tolerances (BASELINE.json)
+
+
+def workload_name():
+    return (f"{'caustic-256 (BASELINE.json configs[3])' if NG == 256 else 'focal-512 (BASELINE.json configs[4])'}: "
+            f"{NG}^3 bump IOR grid, {SENSOR}^2 = {SENSOR * SENSOR} collimated rays in total, ds = h/2, seeds dx=dv=1")
 
 
 def peaks():
@@ -41,6 +60,18 @@ def peaks():
         with open(p) as f:
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def csrc_sha():
+    """Hash of the kernel sources the library is built from; committed ncu counts carry the hash they were
+    captured on (tools/ncu_counts.py)."""
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "adjointnonlinearraytracing_b200", "csrc")
+    for p in sorted(glob.glob(os.path.join(d, "*.cu")) + glob.glob(os.path.join(d, "*.cuh")) + glob.glob(os.path.join(d, "*.h"))):
+        h.update(os.path.basename(p).encode())
+        with open(p, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
 
 
 def workload_host(n_g=None, sensor=None):
@@ -108,38 +139,37 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------- CPU reference arm
-def _cpu_lib():
-    """The reference's own CPU tracer (oracle/_ref) when its build is present, else the C port."""
+def _cpu_lib(h):
+    """The reference's own CPU tracer (oracle/_ref): the build whose rcp(h) is the correctly rounded 1/h when there
+    is one (oracle.ref_for_spacing: what parity is stated against), else any build; else the C port."""
     import oracle
-    if oracle.ref is not None:
-        return oracle.ref, "reference", oracle
+    lib = oracle.ref_for_spacing(h) or oracle.ref
+    if lib is not None:
+        return lib, "reference", oracle
     return oracle.port, "port", oracle
 
 
-def _threads_run(fn, n):
-    out, thr = [None] * n, []
-    def work(i):
-        out[i] = fn(i)
-    for i in range(n):
-        t = threading.Thread(target=work, args=(i,))
-        t.start(); thr.append(t)
-    for t in thr:
-        t.join()
-    return out
+def rel_l2(a, b):
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300))
 
 
 class CpuArm:
-    """Times the reference CPU path on `threads` host threads: rays are split into one strided
-    sub-batch per thread, each thread owns a private gradient grid (the same scheme as the
-    multi-GPU path; the reference itself is single-threaded)."""
+    """Times the reference CPU path on `threads` host threads: the sample (a strided subsample of the benchmarked
+    batch) is split into one strided sub-batch per thread, each thread owns a private gradient grid (the same
+    scheme as the multi-GPU path; the reference itself is single-threaded).  `step()` keeps
+    what it computes -- endpoints and the summed gradient -- for the parity leg."""
 
-    def __init__(self, rays_per_thread=None, threads=None, target_s=2.5):
-        self.lib, self.kind, self.oracle = _cpu_lib()
-        self.rif, self.h, self.ds, pos, vel = workload_host()
+    def __init__(self, rays_per_thread=None, threads=None, target_s=2.5, z0=0.0, host=None):
+        self.rif, self.h, self.ds, pos, vel = host if host is not None else workload_host()
+        self.host = (self.rif, self.h, self.ds, pos, vel)
+        if z0:
+            pos = pos.copy(); pos[:, 2] = np.float32(z0)
+        self.lib, self.kind, self.oracle = _cpu_lib(np.float32(self.h))
         self.threads = threads or max(1, len(os.sched_getaffinity(0)))
         if rays_per_thread is None:  # pilot: size the sample so one step takes ~target_s per thread
-            p = pos[:: max(1, len(pos) // 1024)][:1024]
-            v = vel[:: max(1, len(vel) // 1024)][:1024]
+            p = np.ascontiguousarray(pos[:: max(1, len(pos) // 1024)][:1024])
+            v = np.ascontiguousarray(vel[:: max(1, len(vel) // 1024)][:1024])
             t0 = time.perf_counter()
             xt, vt = self.lib.trace(self.rif, p, v, np.float32(self.h), np.float32(self.ds))
             self.lib.backtrace(self.rif, xt, vt, np.ones_like(p), np.ones_like(p), np.float32(self.h), np.float32(self.ds))
@@ -148,35 +178,46 @@ class CpuArm:
         self.rpt = rays_per_thread
         n = self.rpt * self.threads
         stride = max(1, len(pos) // n)
-        self.pos = [np.ascontiguousarray(pos[i::stride * self.threads][: self.rpt]) for i in range(self.threads)]
-        self.vel = [np.ascontiguousarray(vel[i::stride * self.threads][: self.rpt]) for i in range(self.threads)]
+        self.idx = [np.arange(i, len(pos), stride * self.threads)[: self.rpt] for i in range(self.threads)]
+        self.pos = [np.ascontiguousarray(pos[ix]) for ix in self.idx]
+        self.vel = [np.ascontiguousarray(vel[ix]) for ix in self.idx]
         self.steps = None
+        self.last = None
 
     def count_steps(self):
         port = self.oracle.port
         h, ds = np.float32(self.h), np.float32(self.ds)
-        import ctypes  # each thread needs its own wrapper state (last_steps)
-        def one(i):
+
+        def one(i):  # each thread needs its own wrapper state (last_steps)
             lib = self.oracle._Lib(port.path, "orc_", np.float32, returns_steps=True)
             xt, vt = lib.trace(self.rif, self.pos[i], self.vel[i], h, ds); sf = lib.last_steps
             lib.backtrace(self.rif, xt, vt, np.ones_like(xt), np.ones_like(xt), h, ds); sb = lib.last_steps
             return sf, sb
-        r = _threads_run(one, self.threads)
+        r = self.oracle.run_threads(one, self.threads)
         self.steps = (sum(a for a, _ in r), sum(b for _, b in r))
         return self.steps
 
-    def step(self):
+    def step(self, lib=None, keep=True):
+        lib = lib or self.lib
         h, ds = np.float32(self.h), np.float32(self.ds)
+
         def one(i):
-            xt, vt = self.lib.trace(self.rif, self.pos[i], self.vel[i], h, ds)
-            return self.lib.backtrace(self.rif, xt, vt, np.ones_like(xt), np.ones_like(xt), h, ds)
+            xt, vt = lib.trace(self.rif, self.pos[i], self.vel[i], h, ds)
+            return xt, vt, lib.backtrace(self.rif, xt, vt, np.ones_like(xt), np.ones_like(xt), h, ds)
         t0 = time.perf_counter()
-        _threads_run(one, self.threads)
-        return time.perf_counter() - t0
+        out = self.oracle.run_threads(one, self.threads)
+        dt = time.perf_counter() - t0
+        if keep:
+            g = np.zeros(out[0][2].shape, np.float64)
+            for o in out:
+                g += o[2]
+            self.last = (np.concatenate([o[0] for o in out]), np.concatenate([o[1] for o in out]), g)
+        return dt
 
     def describe(self):
         return (f"{self.threads} threads x {self.rpt} rays (strided subsample of the {SENSOR}^2 batch), "
-                f"{NG}^3 grid, one trace + one backtrace per thread, private gradient grids")
+                f"{NG}^3 grid, one trace + one backtrace per thread, private gradient grids; library "
+                f"{os.path.basename(getattr(self.lib, 'path', '?'))}")
 
 
 def run_reference_arm(args):
@@ -186,21 +227,161 @@ def run_reference_arm(args):
     arm = CpuArm()
     sf, sb = arm.count_steps()
     for _ in range(args.warmup):
-        arm.step()
-    times = [arm.step() for _ in range(args.steps)]
+        arm.step(keep=False)
+    times = [arm.step(keep=False) for _ in range(args.steps)]
     total = sum(times)
     value = (sf + sb) * args.steps / total
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "rays_per_gpu": SENSOR * SENSOR, "grid": [NG, NG, NG],
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(), "rays_total": SENSOR * SENSOR, "grid": [NG, NG, NG],
                    "note": "CPU reference arm: each step is a bounded strided sample of the batch (cpu_baseline.sample)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": arm.threads, "kind": arm.kind, "sample": arm.describe()},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     _emit(line)
+
+
+# --------------------------------------------------------------------------- parity leg (N = 1)
+def parity_leg(arm, ops, torch, dev, rif_dev):
+    """GPU vs the reference library on the sample the cpu_baseline leg just ran (`arm.last`)."""
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    h, ds = arm.h, arm.ds
+
+    def gpu(pos, vel):
+        one = torch.ones(len(pos), 3, device=dev)
+        xt, vt = ops.trace(rif_dev, T(pos), T(vel), h, ds)
+        g = ops.backtrace(rif_dev, xt, vt, one, one, h, ds)
+        return xt.cpu().numpy(), vt.cpu().numpy(), g.cpu().numpy()
+
+    def compare(a, b):
+        e = np.abs(a[0] - b[0]).max(axis=1)
+        return {"rays": int(len(e)), "endpoint_max_abs": float(e.max()), "direction_max_abs": float(np.abs(a[1] - b[1]).max()),
+                "frac_rays_within_1e-5": float(np.mean(e <= END_TOL)),
+                "bit_identical": bool(np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])),
+                "grad_rel_l2": rel_l2(a[2], b[2])}
+
+    pos = np.concatenate(arm.pos); vel = np.concatenate(arm.vel)
+    out = compare(gpu(pos, vel), arm.last)
+    lib = arm.lib
+    out["vs"] = (f"oracle/_ref = the reference's Tracer<false,false> built from /root/reference "
+                 f"({os.path.basename(getattr(lib, 'path', 'port'))}, {lib.isa()}; its rcp(h) "
+                 f"{'==' if lib.rcp(np.float32(h)) == np.float32(1) / np.float32(h) else '!='} the correctly rounded 1/h the kernels use)")
+    out["sample"] = "the cpu_baseline sample: strided subsample of the benchmarked batch (rays ON the z = 0 lattice plane, ds = h/2)"
+    out["tol"] = {"endpoint_abs_unit_span": END_TOL, "grad_rel_l2": GRAD_TOL}
+    ok = out["endpoint_max_abs"] <= END_TOL and out["grad_rel_l2"] <= GRAD_TOL
+    # noise floor: the reference's OTHER ISA build on a quarter of the sample
+    try:
+        builds = arm.oracle.ref_builds()
+        other = [l for l in builds.values() if l.path != getattr(lib, "path", None)]
+        if other and arm.kind == "reference":
+            sub = CpuArm(rays_per_thread=max(1, arm.rpt // 4), threads=arm.threads, host=arm.host)
+            sub.step(lib=lib); a = sub.last
+            sub.step(lib=other[0]); b = sub.last
+            nf = compare(b, a)
+            nf["what"] = (f"the reference against ITSELF: {os.path.basename(other[0].path)} ({other[0].isa()}) vs "
+                          f"{os.path.basename(lib.path)} ({lib.isa()}) on a quarter of the sample -- enoki's rcp(h) differs by one ulp "
+                          "between the builds and every other sample of this batch lies exactly on a cell face")
+            out["noise_floor"] = nf
+    except Exception as e:  # the noise floor is context, never a reason to lose the line
+        out["noise_floor"] = {"error": repr(e)}
+    # backed-off batch: z0 = -0.37 ds, no sample on a lattice plane
+    try:
+        sub = CpuArm(rays_per_thread=max(1, arm.rpt // 4), threads=arm.threads, z0=-0.37 * ds, host=arm.host)
+        sub.step()
+        bo = compare(gpu(np.concatenate(sub.pos), np.concatenate(sub.vel)), sub.last)
+        bo["z0"] = "-0.37 ds"
+        out["backed_off"] = bo
+        ok = ok and bo["endpoint_max_abs"] <= END_TOL and bo["grad_rel_l2"] <= GRAD_TOL
+    except Exception as e:
+        out["backed_off"] = {"error": repr(e)}
+        ok = False
+    out["ok"] = bool(ok)
+    return out
+
+
+# --------------------------------------------------------------------------- the other configurations (N = 1)
+def config_lines(ops, torch, dev):
+    """fwd / adjoint CUDA-event times of BASELINE.json's five configurations (synthetic fields of the named shapes,
+    adjacent to the headline run so they land in the driver-timed line) + the reference's own measurement
+    protocol: 33^3 grid, 512^2 rays, 15 step sizes 0.3 .. 1.2 h (src/test.cpp:148-206)."""
+    from adjointnonlinearraytracing_b200 import scenes as sc
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+
+    def timed(fn, iters):
+        fn(); fn()
+        torch.cuda.synchronize(dev)
+        ts = []
+        for _ in range(iters):
+            a, b = ev(), ev()
+            a.record(); fn(); b.record(); torch.cuda.synchronize(dev)
+            ts.append(a.elapsed_time(b))
+        return float(np.median(ts))
+
+    def bump_dev(ng):  # field A on the device (512^3 takes seconds in numpy)
+        c = torch.arange(ng, device=dev, dtype=torch.float64) / (ng - 1)
+        r2 = ((c - 0.5) ** 2)
+        r2 = r2[:, None, None] + r2[None, :, None] + r2[None, None, :]
+        return (1.0 + 0.2 * torch.exp(-r2 / (2 * 0.2 * 0.2))).to(torch.float32).contiguous()
+
+    out = []
+    for name in sc.CONFIG_NAMES:
+        st = ops.new_stats(dev)
+        if name == "focal512":
+            ng = 512
+            rif = bump_dev(ng); h = float(sc.grid_spacing(ng)); ds = h / 2
+            pos, vel = (T(a) for a in sc.rays_collimated(1448))
+            label = "configs[4] focal stack: 512^3, 1448^2 = 2.1 M rays (one GPU's share of 16.8 M over 8)"
+            kind = "grid"
+        else:
+            case = sc.config_case(name)
+            kind, label = case["kind"], case["label"]
+            rif = T(case["rif"]); pos, vel = T(case["pos"]), T(case["vel"]); ds = float(case["ds"])
+            if kind == "grid":
+                h = float(case["h"])
+        one = torch.ones_like(pos)
+        iters = 5 if pos.shape[0] > 1_000_000 else 20
+        if kind == "grid":
+            xt, vt = ops.trace(rif, pos, vel, h, ds, stats=st); sf = int(st[0]); st.zero_()
+            g = torch.empty_like(rif)
+            ops.backtrace(rif, xt, vt, one, one, h, ds, stats=st, out=g); sb = int(st[0])
+            tf = timed(lambda: ops.trace(rif, pos, vel, h, ds), iters)
+            tb = timed(lambda: ops.backtrace(rif, xt, vt, one, one, h, ds, out=g), iters)
+            grid = list(rif.shape)
+        else:
+            R, L, tgt = case["radius"], case["length"], T(case["target"])
+            xt, vt, _ = ops.trace_cable(rif, R, L, pos, vel, tgt, ds, stats=st); sf = int(st[0]); st.zero_()
+            ops.backtrace_cable(rif, R, L, xt, vt, one, one, ds, stats=st); sb = int(st[0])
+            tf = timed(lambda: ops.trace_cable(rif, R, L, pos, vel, tgt, ds), iters)
+            tb = timed(lambda: ops.backtrace_cable(rif, R, L, xt, vt, one, one, ds), iters)
+            grid = [int(rif.numel())]
+        out.append({"name": name, "label": label, "grid": grid, "rays": int(pos.shape[0]), "fwd_ms": tf, "adj_ms": tb,
+                    "fwd_ray_steps_per_s": sf / (tf * 1e-3), "adj_ray_steps_per_s": sb / (tb * 1e-3),
+                    "ray_steps_per_s": (sf + sb) / ((tf + tb) * 1e-3)})
+        del rif, pos, vel, xt, vt, one
+    # the reference's protocol: 33^3, 512^2 collimated rays from z = 0, step sizes 0.3 .. 1.2 h, all-ones seeds
+    ng = 33
+    rif = T(sc.field_bump(ng)); h = float(sc.grid_spacing(ng))
+    pos, vel = (T(a) for a in sc.rays_collimated(512))
+    one = torch.ones_like(pos); g = torch.empty_like(rif)
+    sweep = []
+    for k in range(15):
+        ds = (0.3 + 0.9 * k / 14) * h
+        st = ops.new_stats(dev)
+        xt, vt = ops.trace(rif, pos, vel, h, ds, stats=st); sf = int(st[0]); st.zero_()
+        ops.backtrace(rif, xt, vt, one, one, h, ds, stats=st, out=g); sb = int(st[0])
+        tf = timed(lambda: ops.trace(rif, pos, vel, h, ds), 10)
+        tb = timed(lambda: ops.backtrace(rif, xt, vt, one, one, h, ds, out=g), 10)
+        sweep.append({"ds_over_h": round(ds / h, 4), "fwd_ms": tf, "adj_ms": tb, "ray_steps_per_s": (sf + sb) / ((tf + tb) * 1e-3)})
+    out.append({"name": "sweep33", "label": "the reference's own protocol (src/test.cpp:148-206): 33^3 grid, 512^2 rays, 15 step sizes "
+                "0.3 .. 1.2 h, trace + backtrace with all-ones seeds",
+                "grid": [ng, ng, ng], "rays": int(pos.shape[0]), "steps": sweep,
+                "ray_steps_per_s_min": min(s["ray_steps_per_s"] for s in sweep),
+                "ray_steps_per_s_max": max(s["ray_steps_per_s"] for s in sweep)})
+    return out
 
 
 # --------------------------------------------------------------------------- GPU arm
@@ -210,7 +391,7 @@ def run_ours(args):
     import __graft_entry__ as ge
     ge.build()
     from adjointnonlinearraytracing_b200 import _capi, ops
-    from adjointnonlinearraytracing_b200.dist import GradAllReduce
+    from adjointnonlinearraytracing_b200.dist import GradAllReduce, shard_bounds
 
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -223,64 +404,116 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     allreduce = GradAllReduce() if world > 1 else None
 
-    rif_h, h, ds, pos_h, vel_h = workload_host()
+    host = workload_host()
+    rif_h, h, ds, pos_h, vel_h = host
     rif = torch.from_numpy(rif_h).to(dev)
-    pos_pin = torch.from_numpy(pos_h).pin_memory()
-    vel_pin = torch.from_numpy(vel_h).pin_memory()
-    pos, vel = pos_pin.to(dev), vel_pin.to(dev)
-    n_rays = pos.shape[0]
-    dx = torch.ones_like(pos); dv = torch.ones_like(pos)
-    grad = torch.empty_like(rif)
-    stats = ops.new_stats(dev)
+    n_total = pos_h.shape[0]
+    strong = args.scaling == "strong"
     flags = 0
+    stats = ops.new_stats(dev)
+    grad = torch.empty_like(rif)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    ev = lambda: torch.cuda.Event(enable_timing=True)
+    def measure(pos_pin, vel_pin, steps, warmup, want_clocks):
+        """Device-resident timing of `steps` steps on this rank's batch -> dict (times are this rank's)."""
+        pos, vel = pos_pin.to(dev), vel_pin.to(dev)
+        dx = torch.ones_like(pos); dv = torch.ones_like(pos)
 
-    def step(timers=None):
-        if timers is not None:
-            timers[0].record()
-        xt, vt = ops.trace(rif, pos, vel, h, ds, flags=flags, stats=stats)
-        if timers is not None:
-            timers[1].record()
-        ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=flags, stats=stats, out=grad)
-        if timers is not None:
-            timers[2].record()
-        if allreduce is not None:
-            allreduce(grad)
-        return xt, vt
+        def step(t=None):
+            if t is not None:
+                t[0].record()
+            xt, vt = ops.trace(rif, pos, vel, h, ds, flags=flags, stats=stats)
+            if t is not None:
+                t[1].record()
+            ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=flags, stats=stats, out=grad)
+            if t is not None:
+                t[2].record()
+            if allreduce is not None:
+                allreduce(grad)
+            if t is not None:
+                t[3].record()
+            return xt, vt
 
-    # ---- device-resident timing ------------------------------------------------
-    for _ in range(max(args.warmup, 3)):
-        step()
-    barrier()
-    stats.zero_()
-    timers = [[ev(), ev(), ev()] for _ in range(args.steps)]
-    launches0 = _capi.launch_count()
-    sampler = ClockSampler(local)
-    t0, t1 = ev(), ev()
-    barrier()
-    sampler.start()
-    t0.record()
-    for k in range(args.steps):
-        step(timers[k])
-    t1.record()
-    barrier()
-    clocks = sampler.stop()
-    launches = _capi.launch_count() - launches0
-    ms = t0.elapsed_time(t1)
-    steps_total = int(stats[0].item())  # live ray-steps of this rank over the K steps
-    fwd_ms = sum(t[0].elapsed_time(t[1]) for t in timers) / args.steps
-    adj_ms = sum(t[1].elapsed_time(t[2]) for t in timers) / args.steps
+        for _ in range(max(warmup, 3)):
+            step()
+        barrier()
+        stats.zero_()
+        timers = [[ev(), ev(), ev(), ev()] for _ in range(steps)]
+        launches0 = _capi.launch_count()
+        sampler = ClockSampler(local) if want_clocks else None
+        t0, t1 = ev(), ev()
+        barrier()
+        if sampler:
+            sampler.start()
+        t0.record()
+        for k in range(steps):
+            step(timers[k])
+        t1.record()
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        r = {"ms": t0.elapsed_time(t1), "launches": _capi.launch_count() - launches0, "clocks": clocks,
+             "steps_total": int(stats[0].item()),
+             "fwd_ms": sum(t[0].elapsed_time(t[1]) for t in timers) / steps,
+             "adj_ms": sum(t[1].elapsed_time(t[2]) for t in timers) / steps,
+             "ar_ms": sum(t[2].elapsed_time(t[3]) for t in timers) / steps}
+        # ray-step split fwd / adjoint (one extra untimed pass each)
+        stats.zero_(); xt, vt = ops.trace(rif, pos, vel, h, ds, flags=flags, stats=stats); r["s_f"] = int(stats[0].item())
+        stats.zero_(); ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=flags, stats=stats, out=grad); r["s_b"] = int(stats[0].item())
+        r["not_exited"] = int(stats[1].item())
+        r["dev"] = (pos, vel, dx, dv)
+        return r
 
-    # ray-step split fwd / adjoint (one extra untimed pass each)
-    stats.zero_(); xt, vt = ops.trace(rif, pos, vel, h, ds, flags=flags, stats=stats); s_f = int(stats[0].item())
-    stats.zero_(); ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=flags, stats=stats, out=grad); s_b = int(stats[0].item())
-    not_exited = int(stats[1].item())
+    def reduce_times(vals):
+        """-> (max over ranks, sum over ranks) of every entry."""
+        t = torch.tensor(vals, dtype=torch.float64, device=dev)
+        if world > 1:
+            mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+            sm = t.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+            return mx.tolist(), sm.tolist()
+        return t.tolist(), t.tolist()
+
+    # ---- this rank's batch ---------------------------------------------------------
+    a, b = shard_bounds(n_total, rank, world) if strong else (0, n_total)
+    pos_pin = torch.from_numpy(np.ascontiguousarray(pos_h[a:b])).pin_memory()
+    vel_pin = torch.from_numpy(np.ascontiguousarray(vel_h[a:b])).pin_memory()
+    n_rays = pos_pin.shape[0]
+
+    m = measure(pos_pin, vel_pin, args.steps, args.warmup, True)
+    pos, vel, dx, dv = m.pop("dev")
+    s_f, s_b = m["s_f"], m["s_b"]
+
+    # ---- N > 1: the summed gradient against a single-GPU gradient of the whole batch ---------
+    grad_check = None
+    if world > 1:
+        xt, vt = ops.trace(rif, pos, vel, h, ds, flags=flags)
+        ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=flags, out=grad)
+        allreduce(grad)
+        det = _capi.DRRT_DETERMINISTIC
+        gdet = ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=det)
+        allreduce(gdet)
+        torch.cuda.synchronize()
+        if rank == 0:
+            if strong:
+                pf, vf = torch.from_numpy(pos_h).to(dev), torch.from_numpy(vel_h).to(dev)
+                scale = 1.0
+            else:  # weak: every rank traced the same batch, the sum is world x one gradient
+                pf, vf, scale = pos, vel, float(world)
+            of = torch.ones_like(pf)
+            xf, vf2 = ops.trace(rif, pf, vf, h, ds, flags=flags)
+            g1 = ops.backtrace(rif, xf, vf2, of, of, h, ds, flags=flags)
+            g1d = ops.backtrace(rif, xf, vf2, of, of, h, ds, flags=det)
+            e = float(((grad.double() - scale * g1.double()).norm() / (scale * g1.double()).norm()).item())
+            ed = float(((gdet.double() - scale * g1d.double()).norm() / (scale * g1d.double()).norm()).item())
+            grad_check = {"rel_l2": e, "deterministic_mode_rel_l2": ed, "tol": 1e-5, "ok": bool(e <= 1e-5 and ed <= 1e-5),
+                          "what": f"all-reduced gradient of {world} ranks vs rank 0's single-GPU gradient of the whole batch "
+                                  f"({pf.shape[0]} rays{', x world' if not strong else ''}); float atomics resp. DRRT_DETERMINISTIC on both sides"}
+            del pf, vf, of, xf, vf2, g1, g1d
+        del xt, vt, gdet
 
     # ---- secondary, labelled: opt-in polynomial arithmetic (NOT a parity mode, DESIGN.md section 4)
     fast = _capi.DRRT_FAST_ARITH
@@ -344,105 +577,150 @@ def run_ours(args):
     assert checksum == args.steps * (s_f + s_b), (checksum, s_f, s_b)
     h2d = pos_pin.numel() * 4 + vel_pin.numel() * 4
     d2h = grad_pin.numel() * 4 + stat_pin.numel() * 8
+    del pipe
 
     # ---- reduce over ranks: max time, sum of work ----------------------------------
-    red = torch.tensor([ms, e2e_ms, float(steps_total), fwd_ms, adj_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        mx = red.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        sm = red.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        ms, e2e_ms, fwd_ms, adj_ms = float(mx[0]), float(mx[1]), float(mx[3]), float(mx[4])
-        steps_all = float(sm[2])
-    else:
-        steps_all = float(steps_total)
+    mx, sm = reduce_times([m["ms"], e2e_ms, float(m["steps_total"]), m["fwd_ms"], m["adj_ms"], m["ar_ms"], e2e_serial_ms,
+                           float(h2d), float(d2h), float(m["launches"])])
+    ms, e2e_ms, fwd_ms, adj_ms, ar_ms, e2e_serial_ms = mx[0], mx[1], mx[3], mx[4], mx[5], mx[6]
+    steps_all = sm[2]
     value = steps_all / (ms * 1e-3)
     e2e_value = steps_all / (e2e_ms * 1e-3)
 
+    # ---- N > 1, strong: the weak figure beside it (4 M rays on every rank) ----------------
+    weak = None
+    if world > 1 and strong:
+        del pos, vel, dx, dv
+        pw = torch.from_numpy(pos_h).pin_memory(); vw = torch.from_numpy(vel_h).pin_memory()
+        wsteps = max(3, args.steps // 4)
+        mw = measure(pw, vw, wsteps, 3, False)
+        mw.pop("dev")
+        wmx, wsm = reduce_times([mw["ms"], float(mw["steps_total"]), mw["ar_ms"]])
+        weak = {"value": wsm[1] / (wmx[0] * 1e-3), "unit": UNIT, "ms_per_step": wmx[0] / wsteps,
+                "rays_per_gpu": n_total, "allreduce_ms_per_step": wmx[2],
+                "note": "weak scaling: every rank traces its own 4 194 304-ray batch (the r01 bench line)"}
+
+    line = None
     if rank == 0:
         peak, peak_src = peaks()
         adj_gbs = BYTES_ADJ * s_b / (adj_ms * 1e-3) / 1e9
         fwd_gbs = BYTES_FWD * s_f / (fwd_ms * 1e-3) / 1e9
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp):
+        sha = csrc_sha()
+
+        def load(name):
             try:
-                traffic = json.load(open(tp)).get("backtrace_kernel_dram_bytes_per_launch")
+                with open(os.path.join(ROOT, "profiles", name)) as f:
+                    return json.load(f)
             except Exception:
-                traffic = None
-        # the adjoint's atomics against the MEASURED L2 sector throughput (tools/l2_probe.cu): the grids are
-        # L2-resident at 256^3, so this is the memory roofline the kernel actually lives under
-        l2 = None
-        lp = os.path.join(ROOT, "profiles", "l2_peaks.json")
-        if os.path.exists(lp) and NG == 256:
-            try:
-                pk = json.load(open(lp))
-                red = pk["backtrace_kernel_l1_red_sectors_per_launch"] / (adj_ms * 1e-3) / 1e9
-                ld = pk["backtrace_kernel_l1_ld_sectors_per_launch"] / (adj_ms * 1e-3) / 1e9
-                l2 = {"red_gsectors_per_s": red, "red_peak_gsectors_per_s": pk["red_scattered_gsectors_per_s"],
-                      "red_frac": red / pk["red_scattered_gsectors_per_s"], "gather_gsectors_per_s": ld,
-                      "gather_peak_gsectors_per_s": pk["gather_scattered_gsectors_per_s"],
-                      "note": "sector counts per launch from the committed ncu capture of this workload, divided by the "
-                              "live kernel time; peaks from profiles/r05_l2_probe.log", "source": pk["source"]}
-            except Exception:
-                l2 = None
-        # what actually bounds the kernels at 256^3: instruction issue / the FP32 pipes.
-        # warp instructions per launch from the committed ncu capture of this workload over the live kernel
-        # times, against 4 schedulers x 1 instruction per clock per SM at the SM clock sampled during the run.
-        issue = None
-        ip = os.path.join(ROOT, "profiles", "issue_counts.json")
-        if os.path.exists(ip) and NG == 256 and clocks and clocks.get("sm_mhz"):
-            try:
-                ic = json.load(open(ip))
-                pk_inst = 148 * 4 * clocks["sm_mhz"] * 1e6 / 1e9
-                fi = ic["trace_kernel_warp_inst_per_launch"] / (fwd_ms * 1e-3) / 1e9
-                ai = ic["backtrace_kernel_warp_inst_per_launch"] / (adj_ms * 1e-3) / 1e9
-                issue = {"unit": "G warp-instructions/s", "peak": pk_inst,
-                         "fwd": {"achieved": fi, "frac": fi / pk_inst, "pipes_pct": ic["trace_kernel_pipes_pct"]},
-                         "adj": {"achieved": ai, "frac": ai / pk_inst, "pipes_pct": ic["backtrace_kernel_pipes_pct"]},
-                         "source": ic["source"]}
-            except Exception:
-                issue = None
+                return None
+
+        counts = load("kernel_counts.json")  # tools/ncu_counts.py: per-launch ncu counters of THIS workload + csrc_sha
+        l2p = load("l2_peaks.json")
+        roof = None
+        if counts is not None and world == 1 and NG == 256:
+            k = counts["backtrace_kernel"]; kf = counts["trace_kernel"]
+            sm_mhz = (m["clocks"] or {}).get("sm_mhz") or counts.get("sm_mhz") or 1965
+            pk_inst = 148 * 4 * sm_mhz * 1e6 / 1e9  # 4 schedulers x 1 warp instruction per clock per SM
+            ai = k["warp_inst"] / (adj_ms * 1e-3) / 1e9
+            fi = kf["warp_inst"] / (fwd_ms * 1e-3) / 1e9
+            roof = {
+                "bound": "issue",
+                "kernel": "backtrace_kernel (adjoint; dominant: %.0f %% of the step)" % (100 * adj_ms / (fwd_ms + adj_ms)),
+                "achieved": ai, "peak": pk_inst, "unit": "G warp-instructions/s", "frac": ai / pk_inst,
+                "peak_source": f"148 SMs x 4 schedulers x 1 warp instruction per clock x {sm_mhz} MHz (SM clock sampled during the timed region)",
+                "why": "both grids are L2-resident at 256^3 (DRAM traffic is ~0.3 % of the algorithmic bytes, see `traffic`), so the "
+                       "kernel is bound by instruction issue / the FP32 pipes; frac = warp instructions per launch (ncu, committed) / "
+                       "live kernel time / issue peak",
+                "traffic": k.get("dram_bytes"),
+                "warp_inst_per_launch": k["warp_inst"], "warp_inst_per_warp_step": k["warp_inst"] / (s_b / 32.0),
+                "threads_per_inst": k.get("threads_per_inst"), "pipes_pct": k.get("pipes_pct"),
+                "fwd_kernel": {"achieved": fi, "frac": fi / pk_inst, "warp_inst_per_launch": kf["warp_inst"],
+                               "warp_inst_per_warp_step": kf["warp_inst"] / (s_f / 32.0),
+                               "threads_per_inst": kf.get("threads_per_inst"), "pipes_pct": kf.get("pipes_pct"),
+                               "traffic": kf.get("dram_bytes")},
+                "counts_source": counts.get("source"), "counts_csrc_sha": counts.get("csrc_sha"), "built_csrc_sha": sha,
+                "stale": bool(counts.get("csrc_sha") != sha),
+            }
+            if l2p is not None and k.get("l1_red_sectors"):
+                red = k["l1_red_sectors"] / (adj_ms * 1e-3) / 1e9
+                roof["l2"] = {"red_gsectors_per_s": red, "red_peak_gsectors_per_s": l2p["red_scattered_gsectors_per_s"],
+                              "red_frac": red / l2p["red_scattered_gsectors_per_s"],
+                              "lts_sectors_per_ray_step": (k.get("lts_sectors") or 0) / s_b,
+                              "note": "RED sectors per launch (ncu) / live kernel time against the measured L2 atomic peak (tools/l2_probe.cu)"}
+        hbm = {"bound": "hbm", "achieved": adj_gbs, "peak": peak, "unit": "GB/s", "frac": adj_gbs / peak, "peak_source": peak_src,
+               "algorithmic_bytes_per_ray_step": BYTES_ADJ,
+               "fwd_kernel": {"achieved": fwd_gbs, "frac": fwd_gbs / peak, "algorithmic_bytes_per_ray_step": BYTES_FWD},
+               "step": {"achieved": (BYTES_FWD * s_f + BYTES_ADJ * s_b) / ((fwd_ms + adj_ms) * 1e-3) / 1e9,
+                        "frac": (BYTES_FWD * s_f + BYTES_ADJ * s_b) / ((fwd_ms + adj_ms) * 1e-3) / 1e9 / peak},
+               "note": "SURVEY section 8d's figure: algorithmic bytes (8 voxel reads [+ 8 atomic adds] x 4 B per ray-step) / kernel "
+                       "time against the measured HBM copy bandwidth.  It can exceed 1: the grids never leave L2, HBM is not the roof."}
+        if roof is None:  # no committed counts for this workload / multi-GPU line: the section-8d figure only
+            roof = dict(hbm)
+            roof["kernel"] = "backtrace_kernel"
+            roof["traffic"] = None
+        else:
+            roof["algorithmic_vs_hbm"] = hbm
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {
-                "workload": WORKLOAD,
-                "rays_per_gpu": n_rays, "grid": [NG, NG, NG], "parallelism": f"rays-dp{world} + grad allreduce" if world > 1 else "single GPU",
+                "workload": workload_name(),
+                "rays_total": n_total * (1 if strong else world), "rays_per_gpu": n_rays, "grid": [NG, NG, NG],
+                "parallelism": (f"rays-dp{world} (contiguous blocks of the one batch) + private gradient grids + one NCCL all-reduce"
+                                if world > 1 else "single GPU"),
                 "l2": (f"no explicit flush: per-step working set (rays in/out {n_rays * 72 / 1e6:.0f} MB + grid {NG ** 3 * 4 / 1e6:.0f} MB + "
                        f"gradient {NG ** 3 * 4 / 1e6:.0f} MB) exceeds the 126 MB L2"
                        + ("; the 67 MB IOR grid staying L2-resident across the step is the design" if NG == 256 else "")),
-                "arithmetic": "exact trajectory (default flags=0): ray path bit-identical to the float32 reference formulas", "ray_steps_fwd": s_f, "ray_steps_adj": s_b,
-                "rays_not_exited": not_exited,
+                "arithmetic": "exact trajectory (default flags=0): ray path bit-identical to the float32 reference formulas",
+                "ray_steps_fwd_rank0": s_f, "ray_steps_adj_rank0": s_b, "rays_not_exited_rank0": m["not_exited"],
             },
             "fwd_ms": fwd_ms, "adj_ms": adj_ms,
             "fwd_ray_steps_per_s": s_f / (fwd_ms * 1e-3), "adj_ray_steps_per_s": s_b / (adj_ms * 1e-3),
-            "roofline": {
-                "bound": "hbm", "kernel": "backtrace_kernel<sdf=0,A_EXACT,AccumFloat> (face-carry flush, no interleave)", "achieved": adj_gbs, "peak": peak,
-                "unit": "GB/s", "frac": adj_gbs / peak, "traffic": traffic, "peak_source": peak_src,
-                "algorithmic_bytes_per_ray_step": BYTES_ADJ, "l2": l2, "issue": issue,
-                "fwd_kernel": {"achieved": fwd_gbs, "frac": fwd_gbs / peak, "algorithmic_bytes_per_ray_step": BYTES_FWD},
-                "step": {"achieved": (BYTES_FWD * s_f + BYTES_ADJ * s_b) / ((fwd_ms + adj_ms) * 1e-3) / 1e9,
-                         "frac": (BYTES_FWD * s_f + BYTES_ADJ * s_b) / ((fwd_ms + adj_ms) * 1e-3) / 1e9 / peak},
-            },
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "roofline": roof,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(sm[7]), "d2h_bytes_per_step": int(sm[8]),
                     "ms_per_step": e2e_ms / args.steps,
-                    "path": "pipeline.HostStepPipeline: pinned host rays -> H2D -> ops.trace -> ops.backtrace -> allreduce -> D2H gradient grid + counters into pinned memory, read on the host every step; depth-2 double buffering on copy-in / compute / copy-out streams",
+                    "path": "pipeline.HostStepPipeline: pinned host rays -> H2D -> ops.trace -> ops.backtrace -> allreduce -> D2H gradient grid + counters into pinned memory, read on the host every step; depth-2 double buffering on copy-in / compute / copy-out streams; bytes are the sum over ranks",
                     "serial_ms_per_step": e2e_serial_ms / args.steps},
-            "gpu_launches": launches, "clocks": clocks,
+            "gpu_launches": int(sm[9]), "clocks": m["clocks"],
             "secondary": {"fast_arith_ms_per_step": fast_ms, "fast_arith_ray_steps_per_s": (s_f + s_b) / (fast_ms * 1e-3),
-                          "note": "DRRT_FAST_ARITH (factored polynomial cell): ray paths differ from the reference at cell faces; not used for value/e2e"},
+                          "note": "DRRT_FAST_ARITH (factored polynomial cell) on rank 0's batch: ray paths differ from the reference at cell faces; not used for value/e2e"},
         }
+        if world > 1:
+            line["allreduce"] = {"ms_per_step": ar_ms, "bytes": NG ** 3 * 4,
+                                 "note": "ncclAllReduce of the gradient grid, CUDA events around the call on the compute stream, max over ranks "
+                                         "(includes waiting for the slowest rank's adjoint)"}
+            line["grad_check"] = grad_check
+            if weak is not None:
+                line["secondary"]["weak"] = weak
         if world == 1 and not args.no_cpu:
-            arm = CpuArm(target_s=8.0)
+            arm = CpuArm(target_s=8.0, host=host)
             sf, sb = arm.count_steps()
             t = arm.step()
             line["cpu_baseline"] = {"value": (sf + sb) / t, "unit": UNIT, "cores": arm.threads, "kind": arm.kind,
                                     "sample": arm.describe(), "seconds": t}
+            try:
+                line["parity"] = parity_leg(arm, ops, torch, dev, rif)
+            except Exception as e:
+                line["parity"] = {"ok": False, "error": repr(e)}
+        if world == 1 and not args.no_configs:
+            try:
+                del grad_pin
+                line["configs"] = config_lines(ops, torch, dev)
+            except Exception as e:
+                line["configs"] = {"error": repr(e)}
         _emit(line)
     if allreduce is not None:
         allreduce.close()
     if world > 1:
         dist.destroy_process_group()
+    if rank == 0:
+        if "parity" in line and not line["parity"].get("ok", False):
+            sys.stderr.write("bench.py: PARITY FAILED: " + json.dumps(line["parity"]) + "\n")
+            sys.exit(3)
+        if grad_check is not None and not grad_check["ok"]:
+            sys.stderr.write("bench.py: GRADIENT CHECK FAILED: " + json.dumps(grad_check) + "\n")
+            sys.exit(4)
 
 
 _REAL_STDOUT = None
@@ -471,17 +749,20 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="N > 1: strong = the configuration as written (one batch of 2048^2 rays sharded over the ranks, default); "
+                         "weak = 2048^2 rays per rank")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline + parity legs")
+    ap.add_argument("--no-configs", action="store_true", help="skip the per-configuration entries")
     ap.add_argument("--workload", default="caustic256", choices=["caustic256", "focal512"],
                     help="caustic256 = BASELINE.json's metric configuration (default, the bench line); focal512 = "
-                         "configs[4]: 512^3 grid, 1448^2 = 2.1 M rays per GPU (16.8 M over 8 GPUs), a labelled extra run")
+                         "configs[4]: 512^3 grid, 4096^2 = 16.8 M rays in total (strong) / 1448^2 = 2.1 M per GPU (weak), a labelled extra run")
     args = ap.parse_args()
     if args.workload == "focal512":
-        global NG, SENSOR, METRIC, WORKLOAD
-        NG, SENSOR = 512, 1448
+        global NG, SENSOR, METRIC
+        NG = 512
+        SENSOR = 4096 if args.scaling == "strong" else 1448
         METRIC = "fwd+adjoint ray-steps/sec at 512^3 grid"
-        WORKLOAD = (f"focal-512 (BASELINE.json configs[4]): {NG}^3 bump IOR grid, {SENSOR}^2 = {SENSOR * SENSOR} "
-                    "collimated rays per GPU, ds = h/2, seeds dx=dv=1")
     _guard_stdout()
     if args.impl == "reference":
         run_reference_arm(args)
