@@ -28,6 +28,7 @@ DRRT_NO_REPLICAS = 1 << 19
 DRRT_FACE_CARRY = 1 << 24
 DRRT_PAIR_RAYS = 1 << 25
 DRRT_NO_PAIR_RAYS = 1 << 26
+DRRT_NO_PHASE_ALIGN = 1 << 27
 DRRT_AGG_RUN_WARP = 15 << 8
 
 
@@ -58,10 +59,10 @@ PROTOTYPES = {
     "drrt_trace_sdf": (c_int, [_P, _P, _I, _I, _I, _P, _P, _L, _I, _F, _F, _P, _P, _P, _U, _P]),
     "drrt_trace_cable": (c_int, [_P, _I, _F, _F, _P, _P, _P, _L, _I, _F, _P, _P, _P, _P, _U, _P]),
     "drrt_backtrace_scratch_bytes": (c_size_t, [_L, _U]),
-    "drrt_backtrace": (c_int, [_P, _I, _I, _I, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, _P, _U, _P]),
-    "drrt_backtrace_sdf": (c_int, [_P, _P, _I, _I, _I, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, _P, _U, _P]),
-    "drrt_backtrace_cable": (c_int, [_P, _I, _F, _F, _P, _P, _P, _P, _L, _I, _F, _P, _P, _P, _U, _P]),
-    "drrt_backtrace_rays": (c_int, [_P, _P, _I, _I, _I, _P, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, _P, _P, _P, _U, _P]),
+    "drrt_backtrace": (c_int, [_P, _I, _I, _I, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, c_size_t, _P, _U, _P]),
+    "drrt_backtrace_sdf": (c_int, [_P, _P, _I, _I, _I, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, c_size_t, _P, _U, _P]),
+    "drrt_backtrace_cable": (c_int, [_P, _I, _F, _F, _P, _P, _P, _P, _L, _I, _F, _P, _P, c_size_t, _P, _U, _P]),
+    "drrt_backtrace_rays": (c_int, [_P, _P, _I, _I, _I, _P, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, _P, _P, c_size_t, _P, _U, _P]),
     "drrt_volume_eval": (c_int, [_P, _I, _I, _I, _P, _L, _I, _F, _P, _P, _P, _U, _P]),
     "drrt_volume_splat": (c_int, [_P, _I, _I, _I, _P, _P, _P, _L, _I, _F, _P]),
     "drrt_cylinder_eval": (c_int, [_P, _I, _F, _F, _P, _L, _I, _P, _P, _P, _P]),

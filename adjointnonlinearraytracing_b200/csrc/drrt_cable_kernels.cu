@@ -239,6 +239,15 @@ int launch_backtrace_cable(bool ref_arith, const CableArgs &a, float *grad, unsi
   int n_sm = a.cable.res <= kCableSmemMax ? a.cable.res : 0;
   if (fixed) {
     AccumFixed acc{fixed, fixed_max_bits, 1.0f};
+    // the int64 copy of a profile with more than 6144 samples exceeds the 48 KiB default of dynamic shared memory
+    static const bool optin = [] {
+      cudaFuncSetAttribute(backtrace_cable_kernel<AccumFixed, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int) (kCableSmemMax * sizeof(unsigned long long)));
+      cudaFuncSetAttribute(backtrace_cable_kernel<AccumFixed, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int) (kCableSmemMax * sizeof(unsigned long long)));
+      return true;
+    }();
+    (void) optin;
     if (ref_arith) backtrace_cable_kernel<AccumFixed, true><<<nb, kAdjThreads, n_sm * sizeof(unsigned long long), s>>>(a, acc);
     else backtrace_cable_kernel<AccumFixed, false><<<nb, kAdjThreads, n_sm * sizeof(unsigned long long), s>>>(a, acc);
   } else {

@@ -183,7 +183,7 @@ int replicas_for_grid(int64_t G, unsigned flags) {
 
 int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, int H, int D,
                      const float *xt, const float *vt, const float *dx, const float *dv, int64_t N,
-                     int layout, float h, float ds, float *grad, void *scratch, int64_t *stats,
+                     int layout, float h, float ds, float *grad, void *scratch, size_t scratch_bytes, int64_t *stats,
                      unsigned flags, cudaStream_t s, const float *pos0 = nullptr, float *dpos = nullptr,
                      float *dvel = nullptr) {
   AdjArgs a;
@@ -197,6 +197,10 @@ int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, i
   const bool det = (flags & DRRT_DETERMINISTIC) != 0;
   const bool accumulate = (flags & DRRT_ACCUMULATE) != 0;
   if (det && !scratch) return fail(DRRT_ERR_INVALID_ARGUMENT, "DRRT_DETERMINISTIC needs a scratch buffer");
+  // The scratch buffer is sized by the caller with drrt_backtrace_scratch_bytes(G, flags) for THIS flag word; a
+  // buffer sized under other flags (e.g. for the int64 grid, then reused for private float copies) is caught here.
+  if (det && scratch_bytes < sizeof(unsigned long long) * (size_t) G + kFixedTail)
+    return fail(DRRT_ERR_INVALID_ARGUMENT, "scratch buffer smaller than drrt_backtrace_scratch_bytes(grid_elems, flags)");
   if (!accumulate) CU_TRY(cudaMemsetAsync(grad, 0, sizeof(float) * (size_t) G, s));  // src/tracer.cpp:401
   if (N == 0) return DRRT_OK;
   if (!xt || !vt || !dx || !dv) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL ray buffer");
@@ -211,6 +215,7 @@ int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, i
   // ds = h/4 7.2 vs 8.9 ms with / without, h/8 12.6 vs 11.1, h/32 39.3 vs 37.4;
   // profiles/r09_facecarry_vs_step.log), so it is chosen from h/ds unless a flag decides.
   a.face_carry = (flags & DRRT_NO_FACE_CARRY) ? 0 : (flags & DRRT_FACE_CARRY) ? 1 : (h < 6.0f * ds ? 1 : 0);
+  a.phase_align = (flags & DRRT_NO_PHASE_ALIGN) ? 0 : 1;
   unsigned long long *fixed = nullptr;
   unsigned *max_bits = nullptr;
   if (det) {
@@ -220,6 +225,11 @@ int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, i
     g_launches += launch_fixed_max(dx, dv, 3 * N, max_bits, s);
   }
   int R = scratch ? replicas_for_grid(G, flags) : 1;
+  if (R > 1 && scratch_bytes < sizeof(float) * (size_t) G * (size_t) (R - 1)) {
+    if ((flags >> 20) & 0xfu)  // DRRT_REPLICAS(n) asked for by the caller: an undersized buffer is an error
+      return fail(DRRT_ERR_INVALID_ARGUMENT, "scratch buffer smaller than drrt_backtrace_scratch_bytes(grid_elems, flags)");
+    R = 1 + (int) (scratch_bytes / (sizeof(float) * (size_t) G));  // the library's own choice: as many copies as fit
+  }
   if (R > 1 && !((flags >> 20) & 0xfu)) {
     const int64_t by_rays = 8 * N / G;
     if (by_rays < R) R = by_rays < 1 ? 1 : (int) by_rays;
@@ -304,33 +314,33 @@ size_t drrt_backtrace_scratch_bytes(int64_t grid_elems, unsigned flags) {
 
 int drrt_backtrace(const float *rif, int W, int H, int D, const float *xt, const float *vt,
                    const float *dx, const float *dv, int64_t N, int layout, float h, float ds,
-                   float *grad, void *scratch, int64_t *stats, unsigned flags,
+                   float *grad, void *scratch, size_t scratch_bytes, int64_t *stats, unsigned flags,
                    drrt_stream_t stream) {
   return backtrace_common(false, rif, nullptr, W, H, D, xt, vt, dx, dv, N, layout, h, ds, grad,
-                          scratch, stats, flags, (cudaStream_t) stream);
+                          scratch, scratch_bytes, stats, flags, (cudaStream_t) stream);
 }
 
 int drrt_backtrace_sdf(const float *rif, const float *sdf, int W, int H, int D, const float *xt,
                        const float *vt, const float *dx, const float *dv, int64_t N, int layout,
-                       float h, float ds, float *grad, void *scratch, int64_t *stats,
+                       float h, float ds, float *grad, void *scratch, size_t scratch_bytes, int64_t *stats,
                        unsigned flags, drrt_stream_t stream) {
   if (!sdf) return fail(DRRT_ERR_INVALID_ARGUMENT, "sdf is NULL");
   return backtrace_common(true, rif, sdf, W, H, D, xt, vt, dx, dv, N, layout, h, ds, grad, scratch,
-                          stats, flags, (cudaStream_t) stream);
+                          scratch_bytes, stats, flags, (cudaStream_t) stream);
 }
 
 int drrt_backtrace_rays(const float *rif, const float *sdf, int W, int H, int D, const float *xt,
                         const float *vt, const float *dx, const float *dv, const float *pos0, int64_t N,
                         int layout, float h, float ds, float *grad, float *dpos, float *dvel,
-                        void *scratch, int64_t *stats, unsigned flags, drrt_stream_t stream) {
+                        void *scratch, size_t scratch_bytes, int64_t *stats, unsigned flags, drrt_stream_t stream) {
   if (N > 0 && (!dpos || !dvel)) return fail(DRRT_ERR_INVALID_ARGUMENT, "dpos / dvel is NULL");
   return backtrace_common(sdf != nullptr, rif, sdf, W, H, D, xt, vt, dx, dv, N, layout, h, ds, grad,
-                          scratch, stats, flags, (cudaStream_t) stream, pos0, dpos, dvel);
+                          scratch, scratch_bytes, stats, flags, (cudaStream_t) stream, pos0, dpos, dvel);
 }
 
 int drrt_backtrace_cable(const float *rif, int res, float radius, float length, const float *xt,
                          const float *vt, const float *dx, const float *dv, int64_t N, int layout,
-                         float ds, float *grad, void *scratch, int64_t *stats, unsigned flags,
+                         float ds, float *grad, void *scratch, size_t scratch_bytes, int64_t *stats, unsigned flags,
                          drrt_stream_t stream) {
   cudaStream_t s = (cudaStream_t) stream;
   CableArgs a;
@@ -342,6 +352,8 @@ int drrt_backtrace_cable(const float *rif, int res, float radius, float length, 
   const bool det = (flags & DRRT_DETERMINISTIC) != 0;
   const bool accumulate = (flags & DRRT_ACCUMULATE) != 0;
   if (det && !scratch) return fail(DRRT_ERR_INVALID_ARGUMENT, "DRRT_DETERMINISTIC needs a scratch buffer");
+  if (det && scratch_bytes < sizeof(unsigned long long) * (size_t) res + kFixedTail)
+    return fail(DRRT_ERR_INVALID_ARGUMENT, "scratch buffer smaller than drrt_backtrace_scratch_bytes(res, flags)");
   if (!accumulate) CU_TRY(cudaMemsetAsync(grad, 0, sizeof(float) * (size_t) res, s));
   if (N == 0) return DRRT_OK;
   if (!xt || !vt || !dx || !dv) return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL ray buffer");

@@ -155,7 +155,7 @@ int drrt_backtrace_host(const float *rif, int W, int H, int D, const float *xt, 
   H_TRY(cudaMemsetAsync(c.stats.p, 0, 2 * sizeof(int64_t), c.stream));
   rc = drrt_backtrace((const float *) c.rif.p, W, H, D, (const float *) c.ray[0].p, (const float *) c.ray[1].p,
                       (const float *) c.ray[2].p, (const float *) c.ray[3].p, N, layout, h, ds,
-                      (float *) c.grad.p, scratch, (int64_t *) c.stats.p, flags, (drrt_stream_t) c.stream);
+                      (float *) c.grad.p, scratch, sb, (int64_t *) c.stats.p, flags, (drrt_stream_t) c.stream);
   if (rc) return rc;
   H_TRY(cudaMemcpyAsync(grad, c.grad.p, gb, cudaMemcpyDeviceToHost, c.stream));
   int64_t st[2] = {0, 0};

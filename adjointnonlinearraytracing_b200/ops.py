@@ -206,6 +206,10 @@ def _scratch(G: int, flags: int, dev):
     return torch.empty(nbytes, dtype=torch.uint8, device=dev) if nbytes else None
 
 
+def _nbytes(t) -> int:
+    return 0 if t is None else int(t.numel() * t.element_size())
+
+
 def _adj_out(out, rif, flags):
     if out is None:
         if flags & DRRT_ACCUMULATE:
@@ -229,7 +233,7 @@ def backtrace(rif, xt, vt, dx, dv, h, ds, *, res=None, flags=0, stats=None, out=
     with torch.cuda.device(dev):
         _capi.check(_capi.load().drrt_backtrace(_ptr(rif), W, H, D, _ptr(xt), _ptr(vt), _ptr(dx), _ptr(dv),
                                                 N, _lay(layout), float(h), float(ds), _ptr(grad),
-                                                _ptr(scratch), _ptr(stats), int(flags), _stream(rif)))
+                                                _ptr(scratch), _nbytes(scratch), _ptr(stats), int(flags), _stream(rif)))
     return grad
 
 
@@ -248,7 +252,7 @@ def backtrace_sdf(rif, sdf, xt, vt, dx, dv, h, ds, *, res=None, flags=0, stats=N
     with torch.cuda.device(dev):
         _capi.check(_capi.load().drrt_backtrace_sdf(_ptr(rif), _ptr(sdf), W, H, D, _ptr(xt), _ptr(vt),
                                                     _ptr(dx), _ptr(dv), N, _lay(layout), float(h),
-                                                    float(ds), _ptr(grad), _ptr(scratch), _ptr(stats),
+                                                    float(ds), _ptr(grad), _ptr(scratch), _nbytes(scratch), _ptr(stats),
                                                     int(flags), _stream(rif)))
     return grad
 
@@ -276,7 +280,7 @@ def backtrace_rays(rif, xt, vt, dx, dv, h, ds, *, pos0=None, sdf=None, res=None,
         _capi.check(_capi.load().drrt_backtrace_rays(_ptr(rif), _ptr(sdf), W, H, D, _ptr(xt), _ptr(vt),
                                                      _ptr(dx), _ptr(dv), _ptr(pos0), N, _lay(layout),
                                                      float(h), float(ds), _ptr(grad), _ptr(dpos),
-                                                     _ptr(dvel), _ptr(scratch), _ptr(stats), int(flags),
+                                                     _ptr(dvel), _ptr(scratch), _nbytes(scratch), _ptr(stats), int(flags),
                                                      _stream(rif)))
     return grad, dpos, dvel
 
@@ -295,7 +299,7 @@ def backtrace_cable(rif, radius, length, xt, vt, dx, dv, ds, *, flags=0, stats=N
     with torch.cuda.device(dev):
         _capi.check(_capi.load().drrt_backtrace_cable(_ptr(rif), rif.numel(), float(radius), float(length),
                                                       _ptr(xt), _ptr(vt), _ptr(dx), _ptr(dv), N,
-                                                      _lay(layout), float(ds), _ptr(grad), _ptr(scratch),
+                                                      _lay(layout), float(ds), _ptr(grad), _ptr(scratch), _nbytes(scratch),
                                                       _ptr(stats), int(flags), _stream(rif)))
     return grad
 

@@ -29,8 +29,33 @@ class FusedAdamState:
         self.exp_avg_sq = torch.zeros_like(n)
 
     def state_dict(self):
-        return {"step": self.step, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq, "lr": self.lr,
-                "betas": self.betas, "eps": self.eps}
+        """The layout ``torch.optim.Adam([n]).state_dict()`` has -- what the reference writes into its checkpoint
+        (core/optimizer.py:73-78) -- so either side can load the other's file."""
+        ref = torch.optim.Adam([torch.zeros(1)], lr=self.lr, betas=self.betas, eps=self.eps)
+        group = {k: v for k, v in ref.state_dict()["param_groups"][0].items()}
+        group.update(lr=self.lr, betas=self.betas, eps=self.eps, params=[0])
+        state = {}
+        if self.step > 0:  # torch creates the per-parameter state on the first step
+            state[0] = {"step": torch.tensor(float(self.step)), "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq}
+        return {"state": state, "param_groups": [group]}
+
+    def load_state_dict(self, sd):
+        """Accepts a ``torch.optim.Adam`` state dict for one parameter (the reference's checkpoint)."""
+        group = sd["param_groups"][0]
+        if len(group["params"]) != 1:
+            raise ValueError("expected the state of a single parameter (the IOR grid)")
+        if group.get("amsgrad", False) or group.get("weight_decay", 0) != 0 or group.get("maximize", False):
+            raise ValueError("FusedAdamState implements plain Adam (no amsgrad / weight decay / maximize)")
+        self.lr, self.betas, self.eps = float(group["lr"]), tuple(group["betas"]), float(group["eps"])
+        st = sd["state"].get(group["params"][0])
+        if st is None:
+            self.step = 0
+            self.exp_avg.zero_(); self.exp_avg_sq.zero_()
+            return
+        if tuple(st["exp_avg"].shape) != tuple(self.exp_avg.shape):
+            raise ValueError("Resolution doesn't match data")
+        self.step = int(st["step"])
+        self.exp_avg.copy_(st["exp_avg"]); self.exp_avg_sq.copy_(st["exp_avg_sq"])
 
     def upres(self, res: int) -> "FusedAdamState":
         new = FusedAdamState.__new__(FusedAdamState)

@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define DRRT_ABI_VERSION 1
+#define DRRT_ABI_VERSION 2
 
 typedef void *drrt_stream_t; /* cudaStream_t */
 
@@ -99,6 +99,9 @@ enum {
    * per two rays; results bit-identical to one ray per thread); DRRT_NO_PAIR_RAYS forces one ray per
    * thread.  Neither bit: the library's choice ("Ray pairs"). */
   DRRT_PAIR_RAYS = 1u << 25,
+  /* Adjoint only, A/B switch: do NOT delay the lanes of a warp that start the backward pass one step out of
+   * phase with their neighbours (the default aligns them so that cell changes coincide; results identical). */
+  DRRT_NO_PHASE_ALIGN = 1u << 27,
   DRRT_NO_PAIR_RAYS = 1u << 26,
   /* Adjoint only: accumulate the gradient in 64-bit fixed point so the result is
    * bit-stable from run to run regardless of atomic ordering (and of the ray
@@ -165,17 +168,17 @@ size_t drrt_backtrace_scratch_bytes(int64_t grid_elems, unsigned flags);
 
 int drrt_backtrace(const float *rif, int W, int H, int D, const float *xt, const float *vt,
                    const float *dx, const float *dv, int64_t N, int layout, float h, float ds,
-                   float *grad, void *scratch, int64_t *stats, unsigned flags,
+                   float *grad, void *scratch, size_t scratch_bytes, int64_t *stats, unsigned flags,
                    drrt_stream_t stream);
 
 int drrt_backtrace_sdf(const float *rif, const float *sdf, int W, int H, int D, const float *xt,
                        const float *vt, const float *dx, const float *dv, int64_t N, int layout,
-                       float h, float ds, float *grad, void *scratch, int64_t *stats,
+                       float h, float ds, float *grad, void *scratch, size_t scratch_bytes, int64_t *stats,
                        unsigned flags, drrt_stream_t stream);
 
 int drrt_backtrace_cable(const float *rif, int res, float radius, float length, const float *xt,
                          const float *vt, const float *dx, const float *dv, int64_t N, int layout,
-                         float ds, float *grad, void *scratch, int64_t *stats, unsigned flags,
+                         float ds, float *grad, void *scratch, size_t scratch_bytes, int64_t *stats, unsigned flags,
                          drrt_stream_t stream);
 
 /* drrt_backtrace_rays <- the ray-state half of ADTracerC.backward / ADSDFTracerC.backward
@@ -190,7 +193,7 @@ int drrt_backtrace_cable(const float *rif, int res, float radius, float length, 
 int drrt_backtrace_rays(const float *rif, const float *sdf, int W, int H, int D, const float *xt,
                         const float *vt, const float *dx, const float *dv, const float *pos0, int64_t N,
                         int layout, float h, float ds, float *grad, float *dpos, float *dvel,
-                        void *scratch, int64_t *stats, unsigned flags, drrt_stream_t stream);
+                        void *scratch, size_t scratch_bytes, int64_t *stats, unsigned flags, drrt_stream_t stream);
 
 /* ---- volume primitives (parity probes; reference src/test.cpp:61-101) -------
  * drrt_volume_eval   <- volume::eval_grad + eval_hess (src/volume.cpp:101-181, :40-99)

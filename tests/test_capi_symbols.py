@@ -22,7 +22,7 @@ def test_header_symbols_exported(cuda_lib):
 def test_python_prototypes_cover_header(cuda_lib):
     from adjointnonlinearraytracing_b200 import _capi
     assert set(declared_symbols()) == set(_capi.PROTOTYPES)
-    assert cuda_lib.drrt_abi_version() == 1
+    assert cuda_lib.drrt_abi_version() == 2
 
 
 def test_library_is_sm100a_only():
@@ -72,10 +72,10 @@ def test_argument_validation_of_the_epilogue_entry_points(cuda_lib):
     assert lib.drrt_plane_source_rand(null, 0, null, 1, 4, 4, 1, 1.0, 0.0, 0, null, 0.0, buf, buf, buf, null, null) == -1
     assert lib.drrt_plane_source_rand(null, 0, null, 0, 4, 4, 1, 1.0, 0.0, 0, null, 0.0, null, null, null, null, null) == 0
     assert lib.drrt_backtrace_rays(buf, null, 4, 4, 4, buf, buf, buf, buf, null, 8, 3, 0.25, 0.125, buf, null, null,
-                                   null, null, 0, null) == -1
+                                   null, 0, null, 0, null) == -1
     assert "dpos" in err()
     assert lib.drrt_backtrace_rays(buf, null, 4, 4, 1, buf, buf, buf, buf, null, 8, 3, 0.25, 0.0, buf, buf, buf,
-                                   null, null, 0, null) < 0
+                                   null, 0, null, 0, null) < 0
     assert lib.drrt_adam_step(buf, buf, buf, buf, 4, 4, 4, 0, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, null) == -1
     # sharded optimiser step: slabs must lie inside the grid, an empty slab is a no-op, 1..16 ranks
     assert lib.drrt_adam_step_slab(buf, buf, buf, buf, 4, 4, 4, 3, 2, 1, 1e-3, 0.9, 0.999, 1e-8, 1.0, 0, null) == -2

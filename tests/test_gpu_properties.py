@@ -239,7 +239,7 @@ def test_private_gradient_copies_only_change_the_summation_order(field, cuda_lib
     out = torch.full_like(rif, 7.0)
     P = lambda t: c_void_p(t.data_ptr())
     rc = lib.drrt_backtrace(P(rif), ng, ng, ng, P(xt), P(vt), P(dx), P(dv), s * s, 3, h, ds, P(out), c_void_p(0),
-                            c_void_p(0), 0, c_void_p(torch.cuda.current_stream().cuda_stream))
+                            0, c_void_p(0), 0, c_void_p(torch.cuda.current_stream().cuda_stream))
     assert rc == 0
     assert rel_l2(out.cpu().numpy(), det.cpu().numpy()) <= 1e-5
     # guard bands around grad and scratch stay untouched (the copies end exactly where scratch_bytes says)
@@ -248,12 +248,27 @@ def test_private_gradient_copies_only_change_the_summation_order(field, cuda_lib
     gbuf = torch.full((G + 2 * pad,), 3.0, device="cuda")
     sbuf = torch.full((nb // 4 + 2 * pad,), 5.0, device="cuda")
     rc = lib.drrt_backtrace(P(rif), ng, ng, ng, P(xt), P(vt), P(dx), P(dv), s * s, 3, h, ds,
-                            c_void_p(gbuf.data_ptr() + 4 * pad), c_void_p(sbuf.data_ptr() + 4 * pad), c_void_p(0), 0,
+                            c_void_p(gbuf.data_ptr() + 4 * pad), c_void_p(sbuf.data_ptr() + 4 * pad), nb, c_void_p(0), 0,
                             c_void_p(torch.cuda.current_stream().cuda_stream))
     assert rc == 0
     assert bool((gbuf[:pad] == 3.0).all()) and bool((gbuf[-pad:] == 3.0).all())
     assert bool((sbuf[:pad] == 5.0).all()) and bool((sbuf[-pad:] == 5.0).all())
     assert rel_l2(gbuf[pad:-pad].view_as(rif).cpu().numpy(), det.cpu().numpy()) <= 1e-5
+    # a scratch buffer sized under OTHER flags: deterministic-sized (8 G + 16 bytes) reused without the flag -> the
+    # library uses only as many private copies as fit; an undersized deterministic buffer is refused
+    nb_det = lib.drrt_backtrace_scratch_bytes(G, DET)
+    sbuf = torch.full((nb_det // 4 + 2 * pad,), 5.0, device="cuda")
+    gbuf.fill_(3.0)
+    rc = lib.drrt_backtrace(P(rif), ng, ng, ng, P(xt), P(vt), P(dx), P(dv), s * s, 3, h, ds,
+                            c_void_p(gbuf.data_ptr() + 4 * pad), c_void_p(sbuf.data_ptr() + 4 * pad), nb_det, c_void_p(0), 0,
+                            c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    assert bool((sbuf[:pad] == 5.0).all()) and bool((sbuf[-pad:] == 5.0).all())
+    assert rel_l2(gbuf[pad:-pad].view_as(rif).cpu().numpy(), det.cpu().numpy()) <= 1e-5
+    rc = lib.drrt_backtrace(P(rif), ng, ng, ng, P(xt), P(vt), P(dx), P(dv), s * s, 3, h, ds,
+                            c_void_p(gbuf.data_ptr() + 4 * pad), c_void_p(sbuf.data_ptr() + 4 * pad), nb_det - 1, c_void_p(0), DET,
+                            c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == -1
     # few rays on the same grid: fewer copies (8 N / G), still the same answer
     few = slice(0, 3000)
     a = ops.backtrace(rif, xt[few].contiguous(), vt[few].contiguous(), dx[few].contiguous(), dv[few].contiguous(), h, ds)

@@ -69,7 +69,7 @@ def test_cuda_step_and_upres_replay_reference_run(cuda_lib):
 
 @pytest.mark.gpu
 def test_multires_opt_drop_in(cuda_lib, tmp_path):
-    from adjointnonlinearraytracing_b200 import optimizer
+    from adjointnonlinearraytracing_b200 import ops, optimizer
     g = load_golden("optim5to9")
     tg = {int(r): torch.from_numpy(g[f"target{int(r)}"]).cuda() for r in g["res_list"]}
     wt = {int(r): torch.from_numpy(g[f"weight{int(r)}"]).cuda() for r in g["res_list"]}
@@ -84,7 +84,25 @@ def test_multires_opt_drop_in(cuda_lib, tmp_path):
     assert np.abs(n.detach().cpu().numpy() - g["final"]).max() <= 2e-6
     assert np.allclose(hist, g["loss_hist"], rtol=1e-5)
     st = torch.load(tmp_path / "state.pt", weights_only=False)
-    assert set(st) == {"rif", "opto_state_dict", "loss_hist"} and st["opto_state_dict"]["step"] == 12
+    assert set(st) == {"rif", "opto_state_dict", "loss_hist"}
+    sd = st["opto_state_dict"]
+    assert int(sd["state"][0]["step"]) == 12 and sd["param_groups"][0]["params"] == [0]
+    # the checkpoint is torch.optim.Adam's own layout (reference core/optimizer.py:73-78): torch loads it ...
+    p = st["rif"].detach().clone().requires_grad_(True)
+    topt = torch.optim.Adam([p], lr=123.0)
+    topt.load_state_dict(sd)
+    assert topt.param_groups[0]["lr"] == float(g["lr"])
+    # ... and the next step of torch.optim.Adam from it equals the fused kernel's next step
+    mine = optimizer.FusedAdamState(p.detach(), lr=0.0)
+    mine.load_state_dict(topt.state_dict())
+    assert mine.step == 12 and mine.lr == float(g["lr"])
+    gr = torch.randn_like(p)
+    p.grad = gr.clone(); topt.step()
+    q = st["rif"].detach().clone()
+    mine.step += 1
+    ops.adam_step_(q, gr, mine.exp_avg, mine.exp_avg_sq, mine.step, mine.lr, mine.betas, mine.eps,
+                   clamp_min=1.0, zero_boundary=False, clamp=False)
+    assert (q - p.detach()).abs().max().item() <= 2e-6
 
 
 @pytest.mark.gpu
@@ -276,3 +294,26 @@ def test_peer_sharded_adam_single_rank_equals_whole_grid(cuda_lib):
         assert torch.equal(n, ref) and torch.equal(opt.exp_avg, m) and torch.equal(opt.exp_avg_sq, v)
     with pytest.raises(RuntimeError):
         PeerShardedAdam(n, torch.zeros(5, 6, 8, device="cuda"), 1e-2)
+
+
+def test_checkpoint_layout_is_torch_adam(tmp_path):
+    """CPU: FusedAdamState.state_dict() has torch.optim.Adam's layout and round-trips through it
+    (reference core/optimizer.py:73-78 saves opto.state_dict())."""
+    from adjointnonlinearraytracing_b200.optimizer import FusedAdamState
+    n = torch.ones(5, 5, 5)
+    a = FusedAdamState(n, lr=3e-3)
+    assert a.state_dict()["state"] == {}  # like torch before the first step
+    a.step = 7
+    a.exp_avg.normal_(); a.exp_avg_sq.uniform_()
+    sd = a.state_dict()
+    ref = torch.optim.Adam([torch.ones(5, 5, 5, requires_grad=True)], lr=1.0)
+    assert set(sd) == set(ref.state_dict()) and set(sd["param_groups"][0]) == set(ref.state_dict()["param_groups"][0])
+    ref.load_state_dict(sd)
+    rs = ref.state_dict()
+    assert rs["param_groups"][0]["lr"] == 3e-3 and float(rs["state"][0]["step"]) == 7.0
+    b = FusedAdamState(n, lr=0.0)
+    b.load_state_dict(rs)
+    assert b.step == 7 and b.lr == 3e-3 and torch.equal(b.exp_avg, a.exp_avg) and torch.equal(b.exp_avg_sq, a.exp_avg_sq)
+    torch.save({"opto_state_dict": sd}, tmp_path / "c.pt")
+    back = torch.load(tmp_path / "c.pt", weights_only=False)["opto_state_dict"]
+    assert torch.equal(back["state"][0]["exp_avg"], a.exp_avg)
