@@ -215,7 +215,6 @@ int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, i
   // ds = h/4 7.2 vs 8.9 ms with / without, h/8 12.6 vs 11.1, h/32 39.3 vs 37.4;
   // profiles/r09_facecarry_vs_step.log), so it is chosen from h/ds unless a flag decides.
   a.face_carry = (flags & DRRT_NO_FACE_CARRY) ? 0 : (flags & DRRT_FACE_CARRY) ? 1 : (h < 6.0f * ds ? 1 : 0);
-  a.phase_align = (flags & DRRT_NO_PHASE_ALIGN) ? 0 : 1;
   unsigned long long *fixed = nullptr;
   unsigned *max_bits = nullptr;
   if (det) {

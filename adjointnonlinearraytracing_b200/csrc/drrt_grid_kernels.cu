@@ -741,46 +741,12 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : 
   f32x2 P[4] = {0ull, 0ull, 0ull, 0ull};  // accumulator pairs (acc[2j], acc[2j+1])
   AggState agg = {1, 0};
   bool have = false;
-  // Phase alignment.  The lanes of a warp were in lock-step in the FORWARD pass (same launch plane, same step
-  // index), so they changed cells on the same iterations; here each lane starts from its own exit sample, and a
-  // lane that needed one more forward step than its neighbour (its first outside sample lies almost a whole step
-  // beyond the face instead of just beyond it) is one iteration out of phase with it for the whole pass -- at
-  // ds = h/2 the two groups then change cells on ALTERNATE iterations and the refill / flush blocks run on every
-  // iteration with half the lanes (profiles/r11_adj_full.txt: 26.2 of 32 threads per instruction, forward 30.4).
-  // tau = overshoot beyond the exit face in units of one step along that axis, in [0, 1]; lanes that crossed the
-  // face at about the same (continuous) time have K - tau equal, K = their forward step count.  When the warp's
-  // taus straddle the wrap (spread smaller after adding 1 to those below 1/2), the lanes with small tau took one
-  // step fewer: they idle for the first iteration, so that every lane is back at the same forward index.
-  int wait = 0;
-  if (!AGG && a.phase_align) {
-    unsigned q = 0xffffffffu;
-    if (valid && active) {
-      float t = -1.f;
-      const float px[3] = {x.x, x.y, x.z}, pv[3] = {v.x, v.y, v.z}, hi[3] = {g.hix, g.hiy, g.hiz};
-#pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        const float o = px[k] >= hi[k] ? px[k] - hi[k] : (px[k] < 0.f ? -px[k] : -1.f);
-        const float st = ds * fabsf(pv[k]);
-        if (o >= 0.f && st > 0.f) t = fmaxf(t, fminf(__fdividef(o, st), 1.f));
-      }
-      if (t >= 0.f) q = (unsigned) (t * 1048576.f);
-    }
-    const bool has = q != 0xffffffffu;
-    const unsigned one = 1048576u, half = 524288u;
-    const unsigned qb = has && q < half ? q + one : q;
-    const unsigned mn_a = __reduce_min_sync(kFull, q), mx_a = __reduce_max_sync(kFull, has ? q : 0u);
-    const unsigned mn_b = __reduce_min_sync(kFull, qb), mx_b = __reduce_max_sync(kFull, has ? qb : 0u);
-    if (mn_a != 0xffffffffu && mx_b - mn_b < mx_a - mn_a && has && q < half) wait = 1;
-  }
-  for (int i = 0;; ++i) {
-    if (AGG) {  // warp-uniform loop (ballots inside): uniform cap
-      if (!__any_sync(kFull, active) || i >= a.max_steps) break;
-    } else if (!active || steps >= a.max_steps) {
+  for (int i = 0; i < a.max_steps; ++i) {
+    if (AGG) {
+      if (!__any_sync(kFull, active)) break;
+    } else if (!active) {
       break;
     }
-    if (wait) {
-      wait = 0;
-    } else {
     CellIdx c = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     bool chg = false;
     if (active) {
@@ -872,7 +838,6 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : 
         }
       }
     }
-    }  // !wait
   }
   if (!REF) {
     bool summed = false;

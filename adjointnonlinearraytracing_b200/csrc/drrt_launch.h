@@ -64,7 +64,6 @@ struct AdjArgs {
   int max_steps;
   int agg_policy;  // warp aggregation: 0 adaptive, 1 off, 2/4/8/32 fixed maximum run length
   int agg_t8, agg_twarp;  // adaptive: lanes per cell from which runs of 8 / the whole warp are summed
-  int phase_align; // delay the lanes of a warp that are one step out of phase (see backtrace_kernel)
   int face_carry;  // keep the accumulators of the face shared with the next cell in registers
   int replicas;    // > 1: CTA b adds into gradient copy b % replicas (copy 0 = grad, the others in `replica_base`)
   float *replica_base;

@@ -99,9 +99,6 @@ enum {
    * per two rays; results bit-identical to one ray per thread); DRRT_NO_PAIR_RAYS forces one ray per
    * thread.  Neither bit: the library's choice ("Ray pairs"). */
   DRRT_PAIR_RAYS = 1u << 25,
-  /* Adjoint only, A/B switch: do NOT delay the lanes of a warp that start the backward pass one step out of
-   * phase with their neighbours (the default aligns them so that cell changes coincide; results identical). */
-  DRRT_NO_PHASE_ALIGN = 1u << 27,
   DRRT_NO_PAIR_RAYS = 1u << 26,
   /* Adjoint only: accumulate the gradient in 64-bit fixed point so the result is
    * bit-stable from run to run regardless of atomic ordering (and of the ray
