@@ -475,7 +475,7 @@ int drrt_source_rand(int kind, const float *offset, uint64_t seed, const float *
                      int P1, int spp, float width, float sensor_dist, float cone_angle_deg, int independent,
                      const float *post_rot, float post_span, float *x, float *v, float *planes, uint8_t *keep,
                      float *tpv, float *target, drrt_stream_t stream) {
-  if (kind < DRRT_SOURCE_PLANE || kind > DRRT_SOURCE_AREA_BIAS)
+  if (kind < DRRT_SOURCE_PLANE || kind > DRRT_SOURCE_POINT_LATTICE)
     return fail(DRRT_ERR_INVALID_ARGUMENT, "ray source: unknown kind");
   if (nviews < 0 || P0 <= 0 || P1 <= 0 || spp <= 0) return fail(DRRT_ERR_INVALID_ARGUMENT, "ray source: bad view / pixel / sample count");
   if (nviews == 0) return DRRT_OK;
@@ -484,6 +484,7 @@ int drrt_source_rand(int kind, const float *offset, uint64_t seed, const float *
   memset(&a, 0, sizeof a);
   a.kind = kind;
   a.cone_cos = (float) cos(0.5 * (double) cone_angle_deg * 3.14159265358979323846 / 180.0);
+  a.cone_half = (float) (0.5 * (double) cone_angle_deg * 3.14159265358979323846 / 180.0);
   a.offset = offset; a.seed = seed; a.P0 = P0; a.P1 = P1; a.spp = spp;
   a.rays_per_view = (int64_t) spp * P0 * P1;
   a.width = width; a.sensor_dist = sensor_dist; a.independent = independent;

@@ -119,6 +119,7 @@ struct SourceArgs {
   float width, sensor_dist;
   int kind;                // DRRT_SOURCE_*
   float cone_cos;          // cone source: cos(cone_angle / 2)
+  float cone_half;         // point lattice: cone_angle / 2 in radians
   int independent;
   int has_post;
   float post_rot[9], post_span;

@@ -4,6 +4,7 @@
 //
 //   plane_source3_rand     reference core/source.py:54-69  (jittered pixel grid on a plane)
 //   point_source3_rand     reference core/source.py:72-104 (point source through a jittered pixel grid)
+//   point_source3          reference core/source.py:29-51  (point source, regular lattice of directions)
 //   cone_source3_rand      reference core/source.py:186-202 + hatbox_sample :531-545 (uniform cone)
 //   area_source3_cone      reference core/source.py:153-183 (cone per jittered pixel; rand_cone_in_sphere)
 //   area_source3_rand_bias reference core/source.py:107-150 (pixel -> random sensor point; rand_area_in_sphere)
@@ -60,7 +61,9 @@ __global__ void __launch_bounds__(256) plane_source_kernel(SourceArgs a) {
   const int i = (int) ((q / a.P1) % a.P0);
   float ua, ub, uc = 0.f, ud = 0.f;
   const bool area = a.kind == DRRT_SOURCE_AREA_CONE || a.kind == DRRT_SOURCE_AREA_BIAS;
-  if (a.offset) {  // torch.rand(2*spp, P0, P1) of this view: [:spp] jitters axis 0, [spp:] axis 1;
+  if (a.kind == DRRT_SOURCE_POINT_LATTICE) {
+    ua = ub = 0.f;  // no jitter: a regular lattice
+  } else if (a.offset) {  // torch.rand(2*spp, P0, P1) of this view: [:spp] jitters axis 0, [spp:] axis 1;
                    // the area sources draw two more planes per view (rand(n) twice / rand(2, n))
     const float *o = a.offset + (int64_t) (a.first_view + view) * (area ? 4 : 2) * a.rays_per_view;
     ua = o[q]; ub = o[a.rays_per_view + q];
@@ -131,7 +134,18 @@ __global__ void __launch_bounds__(256) plane_source_kernel(SourceArgs a) {
     }
   } else {
     f3 d;
-    if (a.kind == DRRT_SOURCE_POINT) {      // point_source3_rand, core/source.py:72-104
+    if (a.kind == DRRT_SOURCE_POINT_LATTICE) {  // point_source3, core/source.py:29-51
+      // theta = linspace(-a, a, P0)[i], phi = linspace(-a, a, P1)[j] (meshgrid 'ij'), the caller passes
+      // P0 = pixels[0] * floor(sqrt(spp)), P1 = pixels[1] * floor(sqrt(spp)), spp = 1 (:30-33)
+      const float ang = a.cone_half;
+      const float th = a.P0 > 1 ? fmaf(2.f * ang, (float) i / (float) (a.P0 - 1), -ang) : -ang;
+      const float ph = a.P1 > 1 ? fmaf(2.f * ang, (float) j / (float) (a.P1 - 1), -ang) : -ang;
+      float st, ct, sp, cp;
+      sincosf(th, &st, &ct); sincosf(ph, &sp, &cp);
+      d = f3{ct * sp, ct * cp, st};                                  // :34-36
+      const float inv = 1.f / sqrtf(d.x * d.x + d.y * d.y + d.z * d.z);  // :40
+      d = f3{d.x * inv, d.y * inv, d.z * inv};
+    } else if (a.kind == DRRT_SOURCE_POINT) {      // point_source3_rand, core/source.py:72-104
       // pixel centres jittered by (u - 0.5) -- not scaled by the pixel size in the reference (:73-79)
       const float pa = w * (((float) i + 0.5f) / (float) a.P0 - 0.5f) + (ua - 0.5f);
       const float pb = w * (((float) j + 0.5f) / (float) a.P1 - 0.5f) + (ub - 0.5f);

@@ -20,7 +20,7 @@ import torch
 
 from . import _capi
 
-__all__ = ["rotation_matrix", "plane_source3_rand", "point_source3_rand", "cone_source3_rand",
+__all__ = ["rotation_matrix", "plane_source3_rand", "point_source3", "point_source3_rand", "cone_source3_rand",
            "area_source3_cone", "area_source3_rand_bias", "rand_cone_in_sphere", "rand_area_in_sphere",
            "rand_rays_in_sphere", "rand_ptrays_in_sphere", "rand_ptcone_in_sphere", "rand_rays_cube",
            "random_rotmat", "random_rotate_ic", "rotate_ray3", "sum_norm"]
@@ -46,7 +46,7 @@ def _fresh_seed() -> int:
     return int(torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).item())
 
 
-PLANE, POINT, CONE, AREA_CONE, AREA_BIAS = 0, 1, 2, 3, 4   # DRRT_SOURCE_* of include/drrt_b200.h
+PLANE, POINT, CONE, AREA_CONE, AREA_BIAS, POINT_LATTICE = 0, 1, 2, 3, 4, 5   # DRRT_SOURCE_* of include/drrt_b200.h
 
 
 def _generate(view_mats, pixels, spp, width, circle, sensor_dist, independent, offset, seed, device, post=None,
@@ -113,6 +113,22 @@ def point_source3_rand(angle, pixels, spp, width, circle=False, xaxis=False, sen
     """reference core/source.py:72-104 -> (x, v, planes): rays from one point through a jittered pixel grid."""
     x, v, planes, _ = _generate([rotation_matrix(angle, xaxis)], pixels, spp, width, circle, sensor_dist, False,
                                 offset, seed, device, kind=POINT)
+    return x, v, planes
+
+
+def _lattice(pixels, spp):
+    """point_source3's direction lattice (reference core/source.py:30-33): per axis pixels * floor(sqrt(spp))."""
+    k = max(int(np.floor(np.sqrt(spp))), 1)
+    return (int(pixels[0]) * k, int(pixels[1]) * k)
+
+
+def point_source3(angle, pixels, spp, width, cone_angle=90, xaxis=False, sensor_dist=0.0, circle=False, *,
+                  device="cuda"):
+    """reference core/source.py:29-51 -> (x, v, planes): a point source on the volume face with a regular lattice of
+    (pixels[0] k) x (pixels[1] k) directions, k = floor(sqrt(spp)); `circle` is accepted and ignored, as in the
+    reference."""
+    x, v, planes, _ = _generate([rotation_matrix(angle, xaxis)], _lattice(pixels, spp), 1, width, False, sensor_dist,
+                                False, None, 0, device, kind=POINT_LATTICE, cone_angle=cone_angle)
     return x, v, planes
 
 
@@ -201,13 +217,13 @@ def _cube_views():
 
 def rand_rays_cube(im_res, spp, width, circle=False, src_type="plane", cone_ang=90, *, offset=None, seed=None,
                    device="cuda", rotmat=None):
-    """reference core/source.py:398-412: 'plane' -> plane_source3_rand, anything but 'plane' / 'point' ->
-    cone_source3_rand(cone_angle=cone_ang) as in the reference; the regular-lattice 'point' source
-    (point_source3, :29-51) is not built.  `rotmat` fuses the ``random_rotate_ic`` that always follows in
-    the reference's drivers (core/luneburg_opt.py:54-56) into the same kernel."""
-    if src_type == "point":
-        raise NotImplementedError("rand_rays_cube: src_type='point' (point_source3) is not implemented on the device")
-    kind = PLANE if src_type == "plane" else CONE
+    """reference core/source.py:398-412: 'plane' -> plane_source3_rand, 'point' -> point_source3(cone_angle=cone_ang)
+    (the regular direction lattice, :29-51), anything else -> cone_source3_rand(cone_angle=cone_ang), as in the
+    reference.  `rotmat` fuses the ``random_rotate_ic`` that always follows in the reference's drivers
+    (core/luneburg_opt.py:54-56) into the same kernel."""
+    kind = PLANE if src_type == "plane" else POINT_LATTICE if src_type == "point" else CONE
+    if kind == POINT_LATTICE:
+        im_res, spp, offset, seed = _lattice(im_res, spp), 1, None, 0
     x, v, planes, nrays = _generate(_cube_views(), im_res, spp, width, circle and kind == PLANE, 0.0, False, offset,
                                     seed, device, post=rotmat, post_span=width, kind=kind, cone_angle=cone_ang)
     return (x, v, planes), nrays

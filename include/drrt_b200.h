@@ -318,7 +318,11 @@ int drrt_plane_source_rand(const float *offset, uint64_t seed, const float *view
  *                      two later draws) and write tpv (N floats: sensor_dist / v.y) and, for
  *                      AREA_BIAS, target (N x 3: the reference's `xt`); both nullable. */
 enum { DRRT_SOURCE_PLANE = 0, DRRT_SOURCE_POINT = 1, DRRT_SOURCE_CONE = 2, DRRT_SOURCE_AREA_CONE = 3,
-       DRRT_SOURCE_AREA_BIAS = 4 };
+       DRRT_SOURCE_AREA_BIAS = 4,
+       /* <- source.point_source3 (core/source.py:29-51, what rand_rays_cube(src_type='point') uses): a point source with
+        * a REGULAR lattice of directions theta_i x phi_j in [-cone_angle/2, cone_angle/2]; no jitter (offset / seed are
+        * ignored).  Pass P0 = pixels[0] * floor(sqrt(spp)), P1 = pixels[1] * floor(sqrt(spp)), spp = 1. */
+       DRRT_SOURCE_POINT_LATTICE = 5 };
 int drrt_source_rand(int kind, const float *offset, uint64_t seed, const float *view_rot, int nviews, int P0,
                      int P1, int spp, float width, float sensor_dist, float cone_angle_deg, int independent,
                      const float *post_rot, float post_span, float *x, float *v, float *planes, uint8_t *keep,

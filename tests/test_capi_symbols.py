@@ -65,7 +65,7 @@ def test_argument_validation_of_the_epilogue_entry_points(cuda_lib):
     assert "dimage" in err()
     assert lib.drrt_sensor_gather(buf, buf, 8, 3, v3, v3, v3, v3, null, 8, 1.0, buf, 0, null) == -1
     assert lib.drrt_sensor_gather(buf, buf, -1, 3, v3, v3, v3, v3, buf, 8, 1.0, buf, 0, null) == -1
-    assert lib.drrt_source_rand(5, null, 0, buf, 1, 4, 4, 1, 1.0, 0.0, 90.0, 0, null, 0.0, buf, buf, buf, null, null, null, null) == -1
+    assert lib.drrt_source_rand(6, null, 0, buf, 1, 4, 4, 1, 1.0, 0.0, 90.0, 0, null, 0.0, buf, buf, buf, null, null, null, null) == -1
     assert "kind" in err()
     assert lib.drrt_source_rand(0, null, 0, buf, 1, 0, 4, 1, 1.0, 0.0, 90.0, 0, null, 0.0, buf, buf, buf, null, null, null,
                                 null) == -1

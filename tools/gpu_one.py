@@ -18,7 +18,19 @@ from tools.gpu_configs import multiview_rays  # noqa: E402
 
 dev = torch.device("cuda:0")
 T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+def tiled(s, tx, ty, fn=sc.rays_collimated, **kw):
+    """The s x s sensor batch re-ordered so that 32 consecutive rays form a tx x ty pixel tile (tx * ty = 32)."""
+    pos, vel = fn(s, **kw)
+    idx = np.arange(s * s).reshape(s // ty, ty, s // tx, tx).transpose(0, 2, 1, 3).reshape(-1)
+    return np.ascontiguousarray(pos[idx]), np.ascontiguousarray(vel[idx])
+
+
 CASES = {
+    "caustic_t8x4": lambda: (256, *tiled(2048, 8, 4)),
+    "caustic_t4x8": lambda: (256, *tiled(2048, 4, 8)),
+    "caustic_t16x2": lambda: (256, *tiled(2048, 16, 2)),
+    "luneburg_t8x4": lambda: (32, *tiled(256, 8, 4)),
+    "lunefield_t8x4": lambda: (32, *tiled(256, 8, 4)),
     "caustic": lambda: (256, *sc.rays_collimated(2048)),
     "cone": lambda: (256, *sc.rays_cone(2048, spread=0.05)),
     "fuel": lambda: (65, *multiview_rays(32, 64, 16)),
@@ -27,7 +39,7 @@ CASES = {
     "lunyaml": lambda: (129, *lunyaml()),
     "lunefield": lambda: (32, *sc.rays_collimated(256)),
 }
-FIELD = {"lunefield": sc.field_luneburg, "lunyaml": sc.field_luneburg}
+FIELD = {"lunefield": sc.field_luneburg, "lunefield_t8x4": sc.field_luneburg, "lunyaml": sc.field_luneburg}
 STEP_RES = {"lunyaml": 32}
 
 
@@ -51,6 +63,10 @@ if __name__ == "__main__":
     a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
     a.record(); xt, vt = ops.trace(rif, pos, vel, h, ds, stats=st); b.record(); torch.cuda.synchronize()
     print(f"{name} ds = h/{step_res} fwd {a.elapsed_time(b):.3f} ms, {int(st[0])} ray-steps, {pos.shape[0]} rays", flush=True)
+    for _ in range(2):
+        a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+        a.record(); ops.trace(rif, pos, vel, h, ds); b.record(); torch.cuda.synchronize()
+    print(f"{name} fwd (warm) {a.elapsed_time(b):.3f} ms", flush=True)
     g0 = None
     for fl in flag_list:
         for _ in range(reps):
