@@ -10,8 +10,6 @@
 // outputs can change again (gathers are masked to 0 outside, so it flies
 // straight away from a convex box).  trace_target is the exception -- see
 // trace_target_tail_kernel.
-#include <atomic>
-
 #include "drrt_device.cuh"
 #include "drrt_launch.h"
 
@@ -653,9 +651,7 @@ __device__ __forceinline__ bool flush_aggregated(const Accum &out, const CellAdd
 // on the device from the batch itself (average number of consecutive rays per
 // cell in a sample), so no host synchronisation is needed.
 // ---------------------------------------------------------------------------
-constexpr int kInterleaveSlots = 64;
 constexpr int kInterleaveMax = 32;
-__device__ int g_interleave_log2[kInterleaveSlots];
 
 __global__ void __launch_bounds__(256) estimate_interleave_kernel(GridP g, const float *pos, int64_t N,
                                                                   int layout, int forced_log2, int *out) {
@@ -936,17 +932,13 @@ int launch_backtrace(bool sdf, int arith, bool warp_agg, int interleave, const A
   int launched = 1;
   a.interleave_log2 = nullptr;
   // interleave: 0 = off, -1 = measured on the device, 2^k = forced
-  if (interleave != 0 && a.N >= 4096) {
-    static std::atomic<unsigned> next_slot{0};
-    int *slots = nullptr;
-    if (cudaGetSymbolAddress((void **) &slots, g_interleave_log2) == cudaSuccess) {
-      int *slot = slots + (next_slot++ % kInterleaveSlots);
-      int forced = -1;
-      if (interleave > 0) { forced = 0; while ((2 << forced) <= interleave && (2 << forced) <= kInterleaveMax) ++forced; }
-      estimate_interleave_kernel<<<1, 256, 0, s>>>(a.grid, a.xt, a.N, a.layout, forced, slot);
-      a.interleave_log2 = slot;
-      ++launched;
-    }
+  int *slot = nullptr;  // per-call, stream-ordered: nothing is shared between calls or streams
+  if (interleave != 0 && a.N >= 4096 && cudaMallocAsync((void **) &slot, sizeof(int), s) == cudaSuccess) {
+    int forced = -1;
+    if (interleave > 0) { forced = 0; while ((2 << forced) <= interleave && (2 << forced) <= kInterleaveMax) ++forced; }
+    estimate_interleave_kernel<<<1, 256, 0, s>>>(a.grid, a.xt, a.N, a.layout, forced, slot);
+    a.interleave_log2 = slot;
+    ++launched;
   }
   if (fixed) {
     // integer accumulation must not depend on how lanes are grouped: no float pre-summation
@@ -963,6 +955,7 @@ int launch_backtrace(bool sdf, int arith, bool warp_agg, int interleave, const A
       else launch_backtrace_acc<false, AccumFloat, false>(arith, a, acc, s);
     }
   }
+  if (slot) cudaFreeAsync(slot, s);
   return launched;
 }
 

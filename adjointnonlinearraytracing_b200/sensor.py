@@ -44,9 +44,11 @@ def get_tan_vecs(n, t=None):
     return t1, t2
 
 
-def _host3(t):
+_PLANE_CACHE = {}
+
+
+def _c3(vals):
     a = (ctypes.c_float * 3)()
-    vals = t.detach().reshape(-1)[:3].to("cpu", torch.float32).tolist()
     a[0], a[1], a[2] = vals
     return a
 
@@ -105,24 +107,44 @@ class _SensorSplat(torch.autograd.Function):
 
 
 def _plane(plane, tangent):
+    """The plane (p, n) and its tangents as host floats for the C ABI.  The four vectors come to the host in ONE
+    copy (one synchronisation, none for host tensors) and are cached per (tensor, version), so a fixed sensor plane
+    costs nothing after its first use.  The plane is a constant of the call: gradients w.r.t. p, n and the tangent
+    are not provided (the reference's torch ops would propagate them; none of its drivers asks for them)."""
     p, n = plane
     if n.dim() != 2 or n.shape[0] != 1:
         raise RuntimeError("generate_sensor: one plane per call, p and n shaped (1, 3) as in the reference")
-    t1, t2 = get_tan_vecs(n, tangent)
-    return _host3(p), _host3(n), _host3(t1), _host3(t2)
+    key = tuple((t.data_ptr(), t._version, str(t.device)) if t is not None else None for t in (p, n, tangent))
+    hit = _PLANE_CACHE.get(key)
+    if hit is None:
+        t1, t2 = get_tan_vecs(n, tangent)
+        rows = torch.stack([t.detach().reshape(-1)[:3].to(torch.float32) for t in (p, n, t1, t2)]).to("cpu").tolist()
+        hit = tuple(_c3(r) for r in rows)
+        if len(_PLANE_CACHE) > 256:
+            _PLANE_CACHE.clear()
+        _PLANE_CACHE[key] = hit
+    return hit
+
+
+def _per_ray_e(e, x):
+    """A learnable SCALAR exposure gets its gradient like in the reference (plain torch ops there): the kernel returns
+    dL/de per ray, the expand's backward sums it."""
+    if isinstance(e, torch.Tensor) and e.numel() == 1 and e.requires_grad:
+        return e.reshape(1).to(device=x.device, dtype=torch.float32).expand(x.shape[0])
+    return e
 
 
 def generate_sensor(rays, e, plane, res, span, tangent=None):
     """reference core/sensor.py:5-28 -> (res, res) image; differentiable w.r.t. the rays (and e)."""
     x, v = rays
-    return _SensorSplat.apply(x, v, e, _plane(plane, tangent), res, span, False)
+    return _SensorSplat.apply(x, v, _per_ray_e(e, x), _plane(plane, tangent), res, span, False)
 
 
 def generate_inf_sensor(rays, e, plane, res, angle_span=120, tangent=None):
     """reference core/sensor.py:31-54 -> (res, res) far-field image over sin(angle) coordinates."""
     x, v = rays
     ang_cut = math.sin(0.5 * math.radians(angle_span))
-    return _SensorSplat.apply(x, v, e, _plane(plane, tangent), res, 2.0 * ang_cut, True)
+    return _SensorSplat.apply(x, v, _per_ray_e(e, x), _plane(plane, tangent), res, 2.0 * ang_cut, True)
 
 
 class _SensorGather(torch.autograd.Function):

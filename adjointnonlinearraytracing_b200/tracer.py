@@ -11,7 +11,8 @@ read off the adjoint's final co-state (``ops.backtrace_rays``); the plane, targe
 cable AD variants return the ``rif`` gradient only, like their ``Back*`` twins.
 
 Differences from the reference that a caller can observe: none in values beyond
-the stated float32 tolerances; ``ctx`` keeps torch tensors instead of enoki arrays
+the stated float32 tolerances; ``ctx`` keeps torch tensors instead of enoki arrays (the forward
+outputs through ``save_for_backward``, so no reference cycle keeps a batch alive until the cyclic GC)
 and there is no ``enoki.cuda_malloc_trim()`` because nothing is pooled outside
 torch's allocator.
 """
@@ -32,12 +33,13 @@ class BackTracerC(torch.autograd.Function):
     def forward(ctx, rif, x, v, h, ds):
         ctx.rif = rif.detach()
         ctx.h, ctx.ds = h, ds
-        ctx.outx, ctx.outv = ops.trace(ctx.rif, x, v, h, ds, flags=FLAGS)
-        return ctx.outx, ctx.outv
+        outx, outv = ops.trace(ctx.rif, x, v, h, ds, flags=FLAGS)
+        ctx.save_for_backward(outx, outv)  # not ctx attributes: output -> grad_fn -> ctx -> output would be a cycle
+        return outx, outv
 
     @staticmethod
     def backward(ctx, grad_x, grad_v):
-        drif = ops.backtrace(ctx.rif, ctx.outx, ctx.outv, grad_x, grad_v, ctx.h, ctx.ds, flags=FLAGS)
+        drif = ops.backtrace(ctx.rif, *ctx.saved_tensors, grad_x, grad_v, ctx.h, ctx.ds, flags=FLAGS)
         return drif, None, None, None, None
 
 
@@ -48,9 +50,10 @@ class BackPlaneTracerC(torch.autograd.Function):
     def forward(ctx, rif, x, v, sp, sn, h, ds):
         ctx.rif = rif.detach()
         ctx.h, ctx.ds = h, ds
-        ctx.outx, ctx.outv, ctx.outmask = ops.trace_pln(ctx.rif, x, v, sp, sn, h, ds, flags=FLAGS)
-        ctx.mark_non_differentiable(ctx.outmask)
-        return ctx.outx, ctx.outv, ctx.outmask
+        outx, outv, outmask = ops.trace_pln(ctx.rif, x, v, sp, sn, h, ds, flags=FLAGS)
+        ctx.mark_non_differentiable(outmask)
+        ctx.save_for_backward(outx, outv)
+        return outx, outv, outmask
 
     @staticmethod
     def backward(ctx, grad_x, grad_v, outmask):
@@ -59,7 +62,7 @@ class BackPlaneTracerC(torch.autograd.Function):
         if outmask is not None and outmask.dtype == torch.bool:
             grad_x = grad_x.clone()
             grad_x[outmask] = 0
-        drif = ops.backtrace(ctx.rif, ctx.outx, ctx.outv, grad_x, grad_v, ctx.h, ctx.ds, flags=FLAGS)
+        drif = ops.backtrace(ctx.rif, *ctx.saved_tensors, grad_x, grad_v, ctx.h, ctx.ds, flags=FLAGS)
         return drif, None, None, None, None, None, None
 
 
@@ -70,12 +73,13 @@ class BackTargetTracerC(torch.autograd.Function):
     def forward(ctx, rif, x, v, sp, h, ds):
         ctx.rif = rif.detach()
         ctx.h, ctx.ds = h, ds
-        ctx.outx, ctx.outv, outdist2 = ops.trace_target(ctx.rif, x, v, sp, h, ds, flags=FLAGS)
-        return ctx.outx, ctx.outv, outdist2
+        outx, outv, outdist2 = ops.trace_target(ctx.rif, x, v, sp, h, ds, flags=FLAGS)
+        ctx.save_for_backward(outx, outv)
+        return outx, outv, outdist2
 
     @staticmethod
     def backward(ctx, grad_x, grad_v, outdist):
-        drif = ops.backtrace(ctx.rif, ctx.outx, ctx.outv, grad_x, grad_v, ctx.h, ctx.ds, flags=FLAGS)
+        drif = ops.backtrace(ctx.rif, *ctx.saved_tensors, grad_x, grad_v, ctx.h, ctx.ds, flags=FLAGS)
         return drif, None, None, None, None, None
 
 
@@ -87,12 +91,13 @@ class BackSDFTracerC(torch.autograd.Function):
         ctx.rif = rif.detach()
         ctx.sdf = sdf.detach()
         ctx.h, ctx.ds = h, ds
-        ctx.outx, ctx.outv = ops.trace_sdf(ctx.rif, ctx.sdf, x, v, h, ds, flags=FLAGS)
-        return ctx.outx, ctx.outv
+        outx, outv = ops.trace_sdf(ctx.rif, ctx.sdf, x, v, h, ds, flags=FLAGS)
+        ctx.save_for_backward(outx, outv)
+        return outx, outv
 
     @staticmethod
     def backward(ctx, grad_x, grad_v):
-        drif = ops.backtrace_sdf(ctx.rif, ctx.sdf, ctx.outx, ctx.outv, grad_x, grad_v, ctx.h, ctx.ds,
+        drif = ops.backtrace_sdf(ctx.rif, ctx.sdf, *ctx.saved_tensors, grad_x, grad_v, ctx.h, ctx.ds,
                                  flags=FLAGS)
         return drif, None, None, None, None, None
 
@@ -104,12 +109,13 @@ class BackCableTracerC(torch.autograd.Function):
     def forward(ctx, rif, radius, length, x, v, sp, ds):
         ctx.rif = rif.detach()
         ctx.radius, ctx.length, ctx.ds = radius, length, ds
-        ctx.outx, ctx.outv, outdist2 = ops.trace_cable(ctx.rif, radius, length, x, v, sp, ds, flags=FLAGS)
-        return ctx.outx, ctx.outv, outdist2
+        outx, outv, outdist2 = ops.trace_cable(ctx.rif, radius, length, x, v, sp, ds, flags=FLAGS)
+        ctx.save_for_backward(outx, outv)
+        return outx, outv, outdist2
 
     @staticmethod
     def backward(ctx, grad_x, grad_v, outdist):
-        drif = ops.backtrace_cable(ctx.rif, ctx.radius, ctx.length, ctx.outx, ctx.outv, grad_x, grad_v,
+        drif = ops.backtrace_cable(ctx.rif, ctx.radius, ctx.length, *ctx.saved_tensors, grad_x, grad_v,
                                    ctx.ds, flags=FLAGS)
         return drif.reshape(ctx.rif.shape), None, None, None, None, None, None
 
@@ -123,16 +129,17 @@ class ADTracerC(torch.autograd.Function):
         ctx.rif = rif.detach()
         ctx.h, ctx.ds = h, ds
         ctx.x0 = x.detach()
-        ctx.outx, ctx.outv = ops.trace(ctx.rif, x, v, h, ds, flags=FLAGS)
-        return ctx.outx, ctx.outv
+        outx, outv = ops.trace(ctx.rif, x, v, h, ds, flags=FLAGS)
+        ctx.save_for_backward(outx, outv)  # not ctx attributes: output -> grad_fn -> ctx -> output would be a cycle
+        return outx, outv
 
     @staticmethod
     def backward(ctx, grad_x, grad_v):
         need_rif, need_x, need_v = ctx.needs_input_grad[:3]
         if not (need_x or need_v):
-            drif = ops.backtrace(ctx.rif, ctx.outx, ctx.outv, grad_x, grad_v, ctx.h, ctx.ds, flags=FLAGS)
+            drif = ops.backtrace(ctx.rif, *ctx.saved_tensors, grad_x, grad_v, ctx.h, ctx.ds, flags=FLAGS)
             return drif, None, None, None, None
-        drif, dx0, dv0 = ops.backtrace_rays(ctx.rif, ctx.outx, ctx.outv, grad_x, grad_v, ctx.h, ctx.ds,
+        drif, dx0, dv0 = ops.backtrace_rays(ctx.rif, *ctx.saved_tensors, grad_x, grad_v, ctx.h, ctx.ds,
                                             pos0=ctx.x0, flags=FLAGS)
         return (drif if need_rif else None, dx0 if need_x else None, dv0 if need_v else None, None, None)
 
@@ -146,17 +153,18 @@ class ADSDFTracerC(torch.autograd.Function):
         ctx.sdf = sdf.detach()
         ctx.h, ctx.ds = h, ds
         ctx.x0 = x.detach()
-        ctx.outx, ctx.outv = ops.trace_sdf(ctx.rif, ctx.sdf, x, v, h, ds, flags=FLAGS)
-        return ctx.outx, ctx.outv
+        outx, outv = ops.trace_sdf(ctx.rif, ctx.sdf, x, v, h, ds, flags=FLAGS)
+        ctx.save_for_backward(outx, outv)
+        return outx, outv
 
     @staticmethod
     def backward(ctx, grad_x, grad_v):
         need_rif, _, need_x, need_v = ctx.needs_input_grad[:4]
         if not (need_x or need_v):
-            drif = ops.backtrace_sdf(ctx.rif, ctx.sdf, ctx.outx, ctx.outv, grad_x, grad_v, ctx.h, ctx.ds,
+            drif = ops.backtrace_sdf(ctx.rif, ctx.sdf, *ctx.saved_tensors, grad_x, grad_v, ctx.h, ctx.ds,
                                      flags=FLAGS)
             return drif, None, None, None, None, None
-        drif, dx0, dv0 = ops.backtrace_rays(ctx.rif, ctx.outx, ctx.outv, grad_x, grad_v, ctx.h, ctx.ds,
+        drif, dx0, dv0 = ops.backtrace_rays(ctx.rif, *ctx.saved_tensors, grad_x, grad_v, ctx.h, ctx.ds,
                                             pos0=ctx.x0, sdf=ctx.sdf, flags=FLAGS)
         return (drif if need_rif else None, None, dx0 if need_x else None, dv0 if need_v else None,
                 None, None)

@@ -14,7 +14,11 @@
  *     core/tracer.py) or DRRT_SOA for [3][N] (enoki's internal layout).
  *   - Functions without the `_host` suffix take DEVICE pointers and enqueue work
  *     on `stream` (a cudaStream_t; NULL = legacy default stream) without
- *     synchronising.  The caller owns every buffer.
+ *     synchronising.  The caller owns every buffer; the only memory the device entry points
+ *     obtain themselves is stream-ordered and short-lived (cudaMallocAsync / cudaFreeAsync on
+ *     `stream`, no synchronisation): 28 N + 16 bytes of per-ray tail state in drrt_trace_plane /
+ *     _target / _sdf (the batch-coupled iterations of the reference, src/tracer.cpp:144-152,
+ *     :216-231, :279-303) and one int for the opt-in ray interleave of drrt_backtrace.
  *   - `_host` functions take HOST pointers (pinned or pageable), copy in, run,
  *     copy out and synchronise before returning.
  *   - Return value: DRRT_OK or a negative error code; drrt_last_error() gives the
@@ -77,7 +81,6 @@ enum {
    *            length for the aggregation; 0 = adaptive (whole warp when all flushing
    *            lanes sit in one cell -- focused beams).
    * bits 12-17 DRRT_INTERLEAVE(n), n in {1,2,4,8,16,32}: fixed interleave; 0 = measured. */
-  DRRT_NO_WARP_AGGREGATION = 0u, /* kept for source compatibility: aggregation is opt-in */
   DRRT_WARP_AGGREGATION = 1u << 4,
   DRRT_NO_INTERLEAVE = 1u << 5,
   /* DRRT_NO_FACE_CARRY: flush all eight corner accumulators on every cell change instead of
