@@ -25,7 +25,23 @@ def tiled(s, tx, ty, fn=sc.rays_collimated, **kw):
     return np.ascontiguousarray(pos[idx]), np.ascontiguousarray(vel[idx])
 
 
+def by_entry_cell(ng, pos, vel):
+    """Rays sorted by the (linear index of the) grid cell through which they enter the volume."""
+    h = 1.0 / (ng - 1)
+    p = pos.astype(np.float64); v = vel.astype(np.float64)
+    safe = np.where(v != 0, v, 1.0)
+    t0 = np.where(v != 0, (0 - p) / safe, -np.inf); t1 = np.where(v != 0, (1 - p) / safe, np.inf)
+    tn = np.maximum(np.minimum(t0, t1).max(axis=1), 0)
+    c = np.clip(np.floor((p + v * (tn[:, None] + 1e-6)) / h).astype(np.int64), 0, ng - 2)
+    idx = np.argsort((c[:, 2] * ng + c[:, 1]) * ng + c[:, 0], kind="stable")
+    return ng, np.ascontiguousarray(pos[idx]), np.ascontiguousarray(vel[idx])
+
+
 CASES = {
+    "fuel_sorted": lambda: by_entry_cell(65, *multiview_rays(32, 64, 16)),
+    "cone15": lambda: (256, *sc.rays_cone(2048, spread=0.15)),
+    "cone15_sorted": lambda: by_entry_cell(256, *sc.rays_cone(2048, spread=0.15)),
+    "lunefield_sorted": lambda: by_entry_cell(32, *sc.rays_collimated(256)),
     "caustic_t8x4": lambda: (256, *tiled(2048, 8, 4)),
     "caustic_t4x8": lambda: (256, *tiled(2048, 4, 8)),
     "caustic_t16x2": lambda: (256, *tiled(2048, 16, 2)),
@@ -39,7 +55,7 @@ CASES = {
     "lunyaml": lambda: (129, *lunyaml()),
     "lunefield": lambda: (32, *sc.rays_collimated(256)),
 }
-FIELD = {"lunefield": sc.field_luneburg, "lunefield_t8x4": sc.field_luneburg, "lunyaml": sc.field_luneburg}
+FIELD = {"lunefield": sc.field_luneburg, "lunefield_sorted": sc.field_luneburg, "lunefield_t8x4": sc.field_luneburg, "lunyaml": sc.field_luneburg}
 STEP_RES = {"lunyaml": 32}
 
 
