@@ -84,6 +84,7 @@ PROTOTYPES = {
     "drrt_comm_init_rank": (c_int, [POINTER(c_void_p), _I, _P, _I]),
     "drrt_comm_destroy": (c_int, [_P]),
     "drrt_allreduce_grad": (c_int, [_P, c_size_t, _P, _P]),
+    "drrt_allreduce_multimem": (c_int, [_P, c_size_t, _I, _I, _P]),
     "drrt_reduce_scatter_grad": (c_int, [_P, c_size_t, _I, _P, _P]),
     "drrt_adam_step_peers": (c_int, [_P, _P, _I, _I, _P, _P, _I, _I, _I, _I, _I, _I, _F, _F, _F, _F, _F, _U, _P]),
     "drrt_ipc_export": (c_int, [_P, _P, _P]),

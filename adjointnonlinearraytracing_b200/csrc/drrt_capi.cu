@@ -611,4 +611,18 @@ int drrt_cylinder_splat(float *data, int res, float radius, float length, const 
   return check_launch("cylinder_splat");
 }
 
+// In-switch sum of the gradient grid (drrt_misc_kernels.cu: allreduce_multimem_kernel).
+int drrt_allreduce_multimem(float *multicast_grad, size_t count, int rank, int nranks, drrt_stream_t stream) {
+  if (!multicast_grad || nranks <= 0 || rank < 0 || rank >= nranks)
+    return fail(DRRT_ERR_INVALID_ARGUMENT, "allreduce_multimem: bad argument");
+  if (count % 4 || ((uintptr_t) multicast_grad & 15))
+    return fail(DRRT_ERR_INVALID_ARGUMENT, "allreduce_multimem: count must be a multiple of 4 floats and the buffer 16-byte aligned");
+  const int64_t n4 = (int64_t) (count / 4);
+  const int64_t per = (n4 + nranks - 1) / nranks;
+  const int64_t first = per * rank;
+  const int64_t mine = first >= n4 ? 0 : (first + per > n4 ? n4 - first : per);
+  g_launches += launch_allreduce_multimem(multicast_grad, first, mine, (cudaStream_t) stream);
+  return check_launch("allreduce_multimem");
+}
+
 }  // extern "C"

@@ -144,6 +144,8 @@ int launch_backtrace_cable(bool ref_arith, const CableArgs &a, float *grad,
 // deterministic mode helpers
 int launch_fixed_max(const float *dx, const float *dv, int64_t n3, unsigned *max_bits,
                      cudaStream_t s);
+// in-switch sum of slab [first4, first4 + count4) (float4 units) of the multicast-mapped gradient grid
+int launch_allreduce_multimem(float *mc, int64_t first4, int64_t count4, cudaStream_t s);
 int launch_reduce_replicas(float *grad, const float *replicas, int64_t G, int extra, cudaStream_t s);
 int launch_fixed_to_float(const unsigned long long *fixed, const unsigned *max_bits, float *grad,
                           int64_t G, bool accumulate, cudaStream_t s);

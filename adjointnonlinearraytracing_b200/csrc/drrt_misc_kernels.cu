@@ -56,6 +56,35 @@ int launch_reduce_replicas(float *grad, const float *replicas, int64_t G, int ex
   return 1;
 }
 
+// ---------------------------------------------------------------------------
+// Gradient sum INSIDE the NVSwitch (the collective of the multi-GPU path as our own kernel).
+// `mc` is the MULTICAST address of the gradient grid: one virtual address bound to every rank's copy of the buffer
+// (NVLink SHARP; the mapping comes from the caller, e.g. torch's symmetric memory).  Rank r owns slab r of the grid: for
+// each float4 of its slab ONE multimem.ld_reduce makes the switch fetch the P copies and return their sum, and ONE
+// multimem.st makes it write the sum back into all P copies.  Per GPU the links carry 1/P of the grid in (sums) and 1/P
+// out (stores) -- against (P-1)/P each way for a ring or the P2P kernel of drrt_adam_step_peers -- and nothing is staged.
+// The caller orders it after every rank's adjoint and before every rank's next read (two barriers on the stream).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(512) allreduce_multimem_kernel(float *mc, int64_t first4, int64_t count4) {
+  const int64_t stride = (int64_t) gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < count4; i += stride) {
+    float *p = mc + 4 * (first4 + i);
+    float a, b, c, d;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(a), "=f"(b), "=f"(c), "=f"(d) : "l"(p) : "memory");
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                 :: "l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+  }
+}
+
+int launch_allreduce_multimem(float *mc, int64_t first4, int64_t count4, cudaStream_t s) {
+  if (count4 <= 0) return 0;
+  int64_t nb = (count4 + 511) / 512;
+  if (nb > 148 * 4) nb = 148 * 4;  // persistent: 4 CTAs of 512 threads per SM
+  allreduce_multimem_kernel<<<(unsigned) nb, 512, 0, s>>>(mc, first4, count4);
+  return 1;
+}
+
 int launch_fixed_to_float(const unsigned long long *fixed, const unsigned *max_bits, float *grad,
                           int64_t G, bool accumulate, cudaStream_t s) {
   if (G <= 0) return 0;

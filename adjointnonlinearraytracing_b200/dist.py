@@ -77,10 +77,74 @@ class GradAllReduce:
             dist.all_reduce(grad, op=dist.ReduceOp.SUM, group=self.group)
         return grad
 
+    def alloc(self, shape, device) -> torch.Tensor:
+        """A gradient grid this collective can reduce (any float32 CUDA tensor; SwitchAllReduce needs its own)."""
+        return torch.empty(tuple(shape), dtype=torch.float32, device=device)
+
     def close(self):
         if self.comm is not None:
             _capi.load().drrt_comm_destroy(self.comm)
             self.comm = None
+
+
+class SwitchAllReduce:
+    """The gradient sum as THIS library's kernel over NVLink SHARP instead of a NCCL call: the gradient grid lives in
+    a buffer that every rank maps at one MULTICAST address, rank r sums slab r of it with ``multimem.ld_reduce`` (the
+    switch fetches the P copies and returns their sum) and broadcasts the result with ``multimem.st``
+    (``drrt_allreduce_multimem``, csrc/drrt_misc_kernels.cu).  Per GPU the links carry 1/P of the grid each way.
+
+    PyTorch's symmetric memory supplies the plumbing only -- the allocation, the multicast mapping and the two
+    stream-ordered barriers around the kernel; single node, needs a multicast-capable NVSwitch fabric.
+    Gradient grids must come from ``alloc()`` (``ops.backtrace(..., out=buf)`` writes straight into them)."""
+
+    def __init__(self, group=None):
+        if not dist.is_initialized():
+            raise RuntimeError("SwitchAllReduce needs an initialised torch.distributed process group")
+        import torch.distributed._symmetric_memory as symm
+        self._symm = symm
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        self.backend = "switch-multimem"
+        self._handles = {}
+        enable = getattr(symm, "enable_symm_mem_for_group", None)
+        if enable is not None:
+            try:
+                enable(self.group.group_name)
+            except Exception:
+                pass  # newer torch enables groups implicitly
+
+    def alloc(self, shape, device) -> torch.Tensor:
+        n = 1
+        for d in shape:
+            n *= int(d)
+        if n % 4:
+            raise RuntimeError("SwitchAllReduce: the grid must hold a multiple of 4 floats")
+        with torch.cuda.device(device):
+            buf = self._symm.empty(n, dtype=torch.float32, device=torch.device(device))
+            hdl = self._symm.rendezvous(buf, self.group.group_name)
+        mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+        if mc == 0:
+            raise RuntimeError("SwitchAllReduce: this fabric / driver exposes no multicast mapping")
+        view = buf.view(*shape)
+        self._handles[view.data_ptr()] = (hdl, mc, buf)
+        return view
+
+    def __call__(self, grad: torch.Tensor) -> torch.Tensor:
+        if self.world == 1:
+            return grad
+        ent = self._handles.get(grad.data_ptr())
+        if ent is None:
+            raise RuntimeError("SwitchAllReduce: grad must be a buffer returned by alloc()")
+        hdl, mc, _ = ent
+        with torch.cuda.device(grad.device):
+            stream = c_void_p(torch.cuda.current_stream(grad.device).cuda_stream)
+            hdl.barrier(channel=0)  # every rank's adjoint has finished writing its copy
+            _capi.check(_capi.load().drrt_allreduce_multimem(c_void_p(mc), grad.numel(), self.rank, self.world, stream))
+            hdl.barrier(channel=1)  # every slab has landed in every copy
+        return grad
+
+    def close(self):
+        self._handles.clear()
 
 
 class ShardedAdam:

@@ -53,7 +53,8 @@ class HostStepPipeline:
         D = self.DEPTH
         self.pos = [torch.empty(n_rays, 3, device=dev) for _ in range(D)]
         self.vel = [torch.empty(n_rays, 3, device=dev) for _ in range(D)]
-        self.grad = [torch.empty_like(rif) for _ in range(D)]
+        alloc = getattr(allreduce, "alloc", None)  # a collective may need the gradient grid in its own buffers
+        self.grad = [alloc(rif.shape, dev) if alloc is not None else torch.empty_like(rif) for _ in range(D)]
         self.stats = [ops.new_stats(dev) for _ in range(D)]
         self.grad_host = [torch.empty(rif.shape, dtype=torch.float32).pin_memory() for _ in range(D)]
         self.stats_host = [torch.empty(2, dtype=torch.int64).pin_memory() for _ in range(D)]

@@ -356,6 +356,12 @@ int drrt_comm_unique_id(char id[DRRT_UNIQUE_ID_BYTES]);
 int drrt_comm_init_rank(void **comm, int nranks, const char id[DRRT_UNIQUE_ID_BYTES], int rank);
 int drrt_comm_destroy(void *comm);
 int drrt_allreduce_grad(float *grad, size_t count, void *comm, drrt_stream_t stream);
+/* The same sum INSIDE the NVSwitch, as this library's own kernel (no NCCL): `multicast_grad` is the multicast
+ * address of the gradient grid -- one virtual address bound to every rank's copy (NVLink SHARP; the caller creates the
+ * mapping, e.g. with torch.distributed._symmetric_memory) -- and rank r sums slab r with multimem.ld_reduce and
+ * broadcasts it with multimem.st.  count % 4 == 0.  The caller must order the call after every rank's adjoint and
+ * before any rank reads the result (a barrier on `stream` on each side); single node. */
+int drrt_allreduce_multimem(float *multicast_grad, size_t count, int rank, int nranks, drrt_stream_t stream);
 /* Sharded optimiser step for grids whose Adam pass is worth splitting (the 512^3
  * configuration): the same bytes on the wire as the all-reduce, 1/nranks of the optimiser work and state.
  *   drrt_reduce_scatter_grad: in place; afterwards grad[rank * slab_count, (rank + 1) * slab_count) holds the
