@@ -403,6 +403,7 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     allreduce = GradAllReduce() if world > 1 else None
+    collective = {"used": "ncclAllReduce (drrt_allreduce_grad)"} if world > 1 else None
 
     host = workload_host()
     rif_h, h, ds, pos_h, vel_h = host
@@ -413,6 +414,46 @@ def run_ours(args):
     stats = ops.new_stats(dev)
     grad = torch.empty_like(rif)
     ev = lambda: torch.cuda.Event(enable_timing=True)
+
+    # ---- N > 1: which collective.  The in-switch sum (our multimem kernel, dist.SwitchAllReduce) is timed against
+    # NCCL's all-reduce on the gradient grid itself and used when it is available, correct and faster. ----------
+    if world > 1 and args.collective != "nccl":
+        try:
+            from adjointnonlinearraytracing_b200.dist import SwitchAllReduce
+            sw = SwitchAllReduce()
+            gsw = sw.alloc(rif.shape, dev)
+
+            def t_coll(fn, buf, iters=10):
+                for _ in range(3):
+                    fn(buf)
+                dist.barrier(); torch.cuda.synchronize()
+                a_, b_ = ev(), ev()
+                a_.record()
+                for _ in range(iters):
+                    fn(buf)
+                b_.record(); torch.cuda.synchronize()
+                t = torch.tensor([a_.elapsed_time(b_) / iters], device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                return float(t)
+            gen = torch.Generator(device=dev).manual_seed(7 + rank)
+            src = torch.randn(rif.shape, device=dev, generator=gen)
+            ref = src.clone(); allreduce(ref)
+            gsw.copy_(src); sw(gsw); torch.cuda.synchronize()
+            err = float(((gsw.double() - ref.double()).norm() / ref.double().norm()).item())
+            t_nccl, t_sw = t_coll(allreduce, ref), t_coll(sw, gsw)
+            okt = torch.tensor([1.0 if err <= 1e-6 else 0.0], device=dev); dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+            use = bool(okt.item() > 0) and (args.collective == "switch" or t_sw < t_nccl)
+            collective.update({"nccl_ms": t_nccl, "switch_multimem_ms": t_sw, "switch_vs_nccl_rel_l2": err,
+                               "note": "64-bit-identical inputs on both: ncclAllReduce vs drrt_allreduce_multimem (multimem.ld_reduce + multimem.st "
+                                       "on the multicast mapping of the gradient grid, two stream barriers included), collective alone, max over ranks"})
+            del src, ref
+            if use:
+                allreduce_nccl, allreduce, grad = allreduce, sw, gsw
+                collective["used"] = "in-switch sum: drrt_allreduce_multimem (dist.SwitchAllReduce)"
+            else:
+                del gsw
+        except Exception as e:  # no multicast fabric / torch without symmetric memory: NCCL it is
+            collective["switch_unavailable"] = repr(e)[:300]
 
     def barrier():
         if world > 1:
@@ -494,8 +535,10 @@ def run_ours(args):
         ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=flags, out=grad)
         allreduce(grad)
         det = _capi.DRRT_DETERMINISTIC
-        gdet = ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=det)
-        allreduce(gdet)
+        gsum = grad.clone()
+        ops.backtrace(rif, xt, vt, dx, dv, h, ds, flags=det, out=grad)  # `grad` is the buffer the collective knows
+        allreduce(grad)
+        gdet = grad.clone()
         torch.cuda.synchronize()
         if rank == 0:
             if strong:
@@ -507,13 +550,13 @@ def run_ours(args):
             xf, vf2 = ops.trace(rif, pf, vf, h, ds, flags=flags)
             g1 = ops.backtrace(rif, xf, vf2, of, of, h, ds, flags=flags)
             g1d = ops.backtrace(rif, xf, vf2, of, of, h, ds, flags=det)
-            e = float(((grad.double() - scale * g1.double()).norm() / (scale * g1.double()).norm()).item())
+            e = float(((gsum.double() - scale * g1.double()).norm() / (scale * g1.double()).norm()).item())
             ed = float(((gdet.double() - scale * g1d.double()).norm() / (scale * g1d.double()).norm()).item())
             grad_check = {"rel_l2": e, "deterministic_mode_rel_l2": ed, "tol": 1e-5, "ok": bool(e <= 1e-5 and ed <= 1e-5),
                           "what": f"all-reduced gradient of {world} ranks vs rank 0's single-GPU gradient of the whole batch "
                                   f"({pf.shape[0]} rays{', x world' if not strong else ''}); float atomics resp. DRRT_DETERMINISTIC on both sides"}
             del pf, vf, of, xf, vf2, g1, g1d
-        del xt, vt, gdet
+        del xt, vt, gdet, gsum
 
     # ---- secondary, labelled: opt-in polynomial arithmetic (NOT a parity mode)
     fast = _capi.DRRT_FAST_ARITH
@@ -667,7 +710,7 @@ def run_ours(args):
             "config": {
                 "workload": workload_name(),
                 "rays_total": n_total * (1 if strong else world), "rays_per_gpu": n_rays, "grid": [NG, NG, NG],
-                "parallelism": (f"rays-dp{world} (contiguous blocks of the one batch) + private gradient grids + one NCCL all-reduce"
+                "parallelism": (f"rays-dp{world} (contiguous blocks of the one batch) + private gradient grids + one gradient sum: {collective['used']}"
                                 if world > 1 else "single GPU"),
                 "l2": (f"no explicit flush: per-step working set (rays in/out {n_rays * 72 / 1e6:.0f} MB + grid {NG ** 3 * 4 / 1e6:.0f} MB + "
                        f"gradient {NG ** 3 * 4 / 1e6:.0f} MB) exceeds the 126 MB L2"
@@ -687,8 +730,8 @@ def run_ours(args):
                           "note": "DRRT_FAST_ARITH (factored polynomial cell) on rank 0's batch: ray paths differ from the reference at cell faces; not used for value/e2e"},
         }
         if world > 1:
-            line["allreduce"] = {"ms_per_step": ar_ms, "bytes": NG ** 3 * 4,
-                                 "note": "ncclAllReduce of the gradient grid, CUDA events around the call on the compute stream, max over ranks "
+            line["allreduce"] = {"ms_per_step": ar_ms, "bytes": NG ** 3 * 4, "collective": collective,
+                                 "note": "the gradient sum inside the timed step, CUDA events around the call on the compute stream, max over ranks "
                                          "(includes waiting for the slowest rank's adjoint)"}
             line["grad_check"] = grad_check
             if weak is not None:
@@ -712,6 +755,8 @@ def run_ours(args):
         _emit(line)
     if allreduce is not None:
         allreduce.close()
+        if "allreduce_nccl" in locals():
+            allreduce_nccl.close()
     if world > 1:
         dist.destroy_process_group()
     if rank == 0:
@@ -752,6 +797,8 @@ def main():
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
                     help="N > 1: strong = the configuration as written (one batch of 2048^2 rays sharded over the ranks, default); "
                          "weak = 2048^2 rays per rank")
+    ap.add_argument("--collective", default="auto", choices=["auto", "nccl", "switch"],
+                    help="N > 1: the gradient sum -- NCCL all-reduce, this library's in-switch multimem kernel, or (auto) whichever is faster here")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline + parity legs")
     ap.add_argument("--no-configs", action="store_true", help="skip the per-configuration entries")
     ap.add_argument("--workload", default="caustic256", choices=["caustic256", "focal512"],
