@@ -1,5 +1,7 @@
 // Small helper kernels: deterministic-mode fixed-point plumbing and the
 // single-evaluation probes of the volume primitives used by the parity tests.
+#include <cstdlib>
+
 #include "drrt_device.cuh"
 #include "drrt_launch.h"
 
@@ -65,23 +67,43 @@ int launch_reduce_replicas(float *grad, const float *replicas, int64_t G, int ex
 // out (stores) -- against (P-1)/P each way for a ring or the P2P kernel of drrt_adam_step_peers -- and nothing is staged.
 // The caller orders it after every rank's adjoint and before every rank's next read (two barriers on the stream).
 // ---------------------------------------------------------------------------
+template <int U>
 __global__ void __launch_bounds__(512) allreduce_multimem_kernel(float *mc, int64_t first4, int64_t count4) {
+  // U independent ld_reduce in flight per thread before the first store: the round trip through the switch is ~2-3 us
   const int64_t stride = (int64_t) gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < count4; i += stride) {
-    float *p = mc + 4 * (first4 + i);
-    float a, b, c, d;
-    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
-                 : "=f"(a), "=f"(b), "=f"(c), "=f"(d) : "l"(p) : "memory");
-    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
-                 :: "l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+  for (int64_t i0 = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i0 < count4; i0 += stride * U) {
+    float a[U], b[U], c[U], d[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = i0 + u * stride;
+      if (i < count4)
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(a[u]), "=f"(b[u]), "=f"(c[u]), "=f"(d[u]) : "l"(mc + 4 * (first4 + i)) : "memory");
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = i0 + u * stride;
+      if (i < count4)
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                     :: "l"(mc + 4 * (first4 + i)), "f"(a[u]), "f"(b[u]), "f"(c[u]), "f"(d[u]) : "memory");
+    }
   }
 }
 
 int launch_allreduce_multimem(float *mc, int64_t first4, int64_t count4, cudaStream_t s) {
   if (count4 <= 0) return 0;
-  int64_t nb = (count4 + 511) / 512;
-  if (nb > 148 * 4) nb = 148 * 4;  // persistent: 4 CTAs of 512 threads per SM
-  allreduce_multimem_kernel<<<(unsigned) nb, 512, 0, s>>>(mc, first4, count4);
+  // dev knobs (tools/gpu_switch_allreduce.py): DRRT_MM_UNROLL in {1,2,4,8}, DRRT_MM_CTAS per SM
+  static const int unroll = [] { const char *e = getenv("DRRT_MM_UNROLL"); return e ? atoi(e) : 4; }();
+  static const int ctas = [] { const char *e = getenv("DRRT_MM_CTAS"); return e ? atoi(e) : 4; }();
+  int64_t nb = (count4 + 512 * unroll - 1) / (512 * unroll);
+  if (nb > 148 * ctas) nb = 148 * ctas;
+  if (nb < 1) nb = 1;
+  switch (unroll) {
+    case 1: allreduce_multimem_kernel<1><<<(unsigned) nb, 512, 0, s>>>(mc, first4, count4); break;
+    case 2: allreduce_multimem_kernel<2><<<(unsigned) nb, 512, 0, s>>>(mc, first4, count4); break;
+    case 8: allreduce_multimem_kernel<8><<<(unsigned) nb, 512, 0, s>>>(mc, first4, count4); break;
+    default: allreduce_multimem_kernel<4><<<(unsigned) nb, 512, 0, s>>>(mc, first4, count4); break;
+  }
   return 1;
 }
 

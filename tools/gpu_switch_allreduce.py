@@ -42,7 +42,7 @@ def timed(fn, iters=20):
     return float(t)
 
 
-for ng in (256, 512):
+for ng in ((256,) if os.environ.get('DRRT_MM_UNROLL') else (256, 512)):
     shape = (ng, ng, ng)
     try:
         buf = sw.alloc(shape, dev)
@@ -62,7 +62,7 @@ for ng in (256, 512):
     t_s = timed(lambda: sw(buf))
     if rank == 0:
         gb = ng ** 3 * 4 / 1e9
-        print(f"{ng}^3 ({gb * 1e3:.0f} MB) on {world} GPUs: NCCL all-reduce {t_n:.3f} ms | in-switch multimem kernel {t_s:.3f} ms "
+        print(f"[unroll {os.environ.get('DRRT_MM_UNROLL', 'default')} ctas/SM {os.environ.get('DRRT_MM_CTAS', 'default')}] {ng}^3 ({gb * 1e3:.0f} MB) on {world} GPUs: NCCL all-reduce {t_n:.3f} ms | in-switch multimem kernel {t_s:.3f} ms "
               f"(incl. 2 barriers) | rel L2 vs NCCL {err:.1e} | identical on all ranks: {ident} | "
               f"algorithmic {gb / (t_s * 1e-3):.0f} GB/s", flush=True)
     del buf, src, ref, same_everywhere
