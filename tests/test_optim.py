@@ -317,3 +317,73 @@ def test_checkpoint_layout_is_torch_adam(tmp_path):
     torch.save({"opto_state_dict": sd}, tmp_path / "c.pt")
     back = torch.load(tmp_path / "c.pt", weights_only=False)["opto_state_dict"]
     assert torch.equal(back["state"][0]["exp_avg"], a.exp_avg)
+
+
+def _switch_allreduce_worker(rank, world, port, out_dir):
+    import os, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from adjointnonlinearraytracing_b200.dist import GradAllReduce, SwitchAllReduce
+        nccl = GradAllReduce()
+        res = [0.0, 0.0, 0.0]
+        try:
+            sw = SwitchAllReduce()
+            buf = sw.alloc((24, 20, 32), torch.device("cuda", rank))
+        except Exception:  # noqa: BLE001 -- no multicast fabric on this box
+            np.save(os.path.join(out_dir, f"sw{rank}.npy"), np.array([-1.0, 0, 0]))
+            return
+        gen = torch.Generator(device="cuda").manual_seed(5 + rank)
+        for it in range(3):
+            src = torch.randn(buf.shape, device="cuda", generator=gen)
+            ref = src.clone(); nccl(ref)
+            buf.copy_(src); sw(buf)
+            torch.cuda.synchronize()
+            res[0] = max(res[0], float((buf - ref).abs().max()))
+            other = buf.clone(); dist.broadcast(other, 0)
+            res[1] = max(res[1], float((other - buf).abs().max()))
+        res[2] = 1.0
+        try:
+            sw(torch.zeros(24, 20, 32, device="cuda"))  # not a buffer of alloc(): refused
+            res[2] = 0.0
+        except RuntimeError:
+            pass
+        np.save(os.path.join(out_dir, f"sw{rank}.npy"), np.array(res))
+        sw.close(); nccl.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(300)
+def test_switch_allreduce_two_gpus(cuda_lib, tmp_path):
+    """The in-switch gradient sum (multimem.ld_reduce / multimem.st kernel over the multicast mapping) against NCCL's
+    all-reduce: same values (2 ranks: bit-identical), identical on every rank; needs 2 GPUs behind a multicast-capable
+    NVSwitch (skipped otherwise)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import socket
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+    mp.spawn(_switch_allreduce_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    for r in range(2):
+        e = np.load(tmp_path / f"sw{r}.npy")
+        if e[0] < 0:
+            pytest.skip("no multicast mapping on this fabric")
+        assert e[0] <= 1e-6 and e[1] == 0 and e[2] == 1, (r, e)
+
+
+def test_switch_allreduce_argument_checks(cuda_lib):
+    """C ABI error paths of drrt_allreduce_multimem (no GPU needed)."""
+    import ctypes
+    lib = cuda_lib
+    buf = ctypes.c_void_p(256)
+    assert lib.drrt_allreduce_multimem(None, 16, 0, 2, None) == -1
+    assert lib.drrt_allreduce_multimem(buf, 16, 2, 2, None) == -1
+    assert lib.drrt_allreduce_multimem(buf, 18, 0, 2, None) == -1
+    assert lib.drrt_allreduce_multimem(ctypes.c_void_p(260), 16, 0, 2, None) == -1
