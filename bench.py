@@ -358,9 +358,23 @@ def config_lines(ops, torch, dev):
             tf = timed(lambda: ops.trace_cable(rif, R, L, pos, vel, tgt, ds), iters)
             tb = timed(lambda: ops.backtrace_cable(rif, R, L, xt, vt, one, one, ds), iters)
             grid = [int(rif.numel())]
-        out.append({"name": name, "label": label, "grid": grid, "rays": int(pos.shape[0]), "fwd_ms": tf, "adj_ms": tb,
-                    "fwd_ray_steps_per_s": sf / (tf * 1e-3), "adj_ray_steps_per_s": sb / (tb * 1e-3),
-                    "ray_steps_per_s": (sf + sb) / ((tf + tb) * 1e-3)})
+        entry = {"name": name, "label": label, "grid": grid, "rays": int(pos.shape[0]), "fwd_ms": tf, "adj_ms": tb,
+                 "fwd_ray_steps_per_s": sf / (tf * 1e-3), "adj_ray_steps_per_s": sb / (tb * 1e-3),
+                 "ray_steps_per_s": (sf + sb) / ((tf + tb) * 1e-3)}
+        if kind == "grid" and pos.shape[0] <= 300_000:
+            # the small configurations as ONE CUDA graph replay (pipeline.GraphedStep: trace -> seeds -> backtrace), which
+            # takes the host's launch path out of a step that lasts 0.1 - 0.6 ms
+            try:
+                from adjointnonlinearraytracing_b200.pipeline import GraphedStep
+                gs = GraphedStep(rif, h, ds, int(pos.shape[0]))
+                gs.step(pos, vel)
+                tg = timed(lambda: gs.step(), iters)
+                entry["graphed_step_ms"] = tg
+                entry["graphed_ray_steps_per_s"] = (sf + sb) / (tg * 1e-3)
+                del gs
+            except Exception as e:
+                entry["graphed_step_error"] = repr(e)[:200]
+        out.append(entry)
         del rif, pos, vel, xt, vt, one
     # the reference's protocol: 33^3, 512^2 collimated rays from z = 0, step sizes 0.3 .. 1.2 h, all-ones seeds
     ng = 33
