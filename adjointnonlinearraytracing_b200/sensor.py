@@ -11,6 +11,7 @@ from __future__ import annotations
 
 import ctypes
 import math
+import weakref
 from ctypes import c_void_p
 
 import torch
@@ -108,22 +109,28 @@ class _SensorSplat(torch.autograd.Function):
 
 def _plane(plane, tangent):
     """The plane (p, n) and its tangents as host floats for the C ABI.  The four vectors come to the host in ONE
-    copy (one synchronisation, none for host tensors) and are cached per (tensor, version), so a fixed sensor plane
+    copy (one synchronisation, none for host tensors) and are cached per (tensor object, version), so a fixed sensor plane
     costs nothing after its first use.  The plane is a constant of the call: gradients w.r.t. p, n and the tangent
     are not provided (the reference's torch ops would propagate them; none of its drivers asks for them)."""
     p, n = plane
     if n.dim() != 2 or n.shape[0] != 1:
         raise RuntimeError("generate_sensor: one plane per call, p and n shaped (1, 3) as in the reference")
-    key = tuple((t.data_ptr(), t._version, str(t.device)) if t is not None else None for t in (p, n, tangent))
+    ts = (p, n, tangent)
+    key = tuple(id(t) for t in ts)
     hit = _PLANE_CACHE.get(key)
-    if hit is None:
-        t1, t2 = get_tan_vecs(n, tangent)
-        rows = torch.stack([t.detach().reshape(-1)[:3].to(torch.float32) for t in (p, n, t1, t2)]).to("cpu").tolist()
-        hit = tuple(_c3(r) for r in rows)
-        if len(_PLANE_CACHE) > 256:
-            _PLANE_CACHE.clear()
-        _PLANE_CACHE[key] = hit
-    return hit
+    if hit is not None:  # the same tensor OBJECTS (ids are only unique among live objects: check through weakrefs) at the same version
+        refs, versions, val = hit
+        if all((r is None and t is None) or (r is not None and r() is t) for r, t in zip(refs, ts)) and \
+                versions == tuple(t._version if t is not None else -1 for t in ts):
+            return val
+    t1, t2 = get_tan_vecs(n, tangent)
+    rows = torch.stack([t.detach().reshape(-1)[:3].to(torch.float32) for t in (p, n, t1, t2)]).to("cpu").tolist()
+    val = tuple(_c3(r) for r in rows)
+    if len(_PLANE_CACHE) > 256:
+        _PLANE_CACHE.clear()
+    _PLANE_CACHE[key] = (tuple(weakref.ref(t) if t is not None else None for t in ts),
+                         tuple(t._version if t is not None else -1 for t in ts), val)
+    return val
 
 
 def _per_ray_e(e, x):
