@@ -87,6 +87,7 @@ PROTOTYPES = {
     "drrt_allreduce_multimem": (c_int, [_P, c_size_t, _I, _I, _P]),
     "drrt_reduce_scatter_grad": (c_int, [_P, c_size_t, _I, _P, _P]),
     "drrt_adam_step_peers": (c_int, [_P, _P, _I, _I, _P, _P, _I, _I, _I, _I, _I, _I, _F, _F, _F, _F, _F, _U, _P]),
+    "drrt_adam_step_multimem": (c_int, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _F, _F, _F, _F, _U, _P]),
     "drrt_ipc_export": (c_int, [_P, _P, _P]),
     "drrt_ipc_open": (c_int, [_P, ctypes.c_uint64, _P]),
     "drrt_ipc_close_all": (c_int, []),

@@ -551,6 +551,25 @@ int drrt_adam_step_peers(float *const *n_replicas, const float *const *grad_repl
   return check_launch("adam_step_peers");
 }
 
+int drrt_adam_step_multimem(float *n_multicast, const float *grad_multicast, const float *n_local, float *exp_avg_slab,
+                            float *exp_avg_sq_slab, int S0, int S1, int S2, int i0_begin, int i0_count, int step, float lr,
+                            float beta1, float beta2, float eps, float clamp_min, unsigned flags, drrt_stream_t stream) {
+  if (S0 <= 0 || S1 <= 0 || S2 <= 0) return fail(DRRT_ERR_RESOLUTION, "Resolution doesn't match data");
+  if (i0_begin < 0 || i0_count < 0 || (int64_t) i0_begin + i0_count > S0)
+    return fail(DRRT_ERR_RESOLUTION, "slab outside the grid");
+  if (i0_count == 0) return DRRT_OK;
+  if (!n_multicast || !grad_multicast || !n_local || !exp_avg_slab || !exp_avg_sq_slab)
+    return fail(DRRT_ERR_INVALID_ARGUMENT, "NULL grid buffer");
+  if (step < 1) return fail(DRRT_ERR_INVALID_ARGUMENT, "step counts from 1 (torch.optim.Adam)");
+  int r = launch_adam_step_multimem(n_multicast, grad_multicast, n_local, exp_avg_slab, exp_avg_sq_slab, S0, S1, S2, i0_begin,
+                                    i0_count, step, lr, beta1, beta2, eps, clamp_min, !(flags & DRRT_ADAM_KEEP_BOUNDARY),
+                                    !(flags & DRRT_ADAM_NO_CLAMP), (cudaStream_t) stream);
+  if (r == -2) return fail(DRRT_ERR_INVALID_ARGUMENT, "adam_step_multimem: rows of a multiple of 4 floats, 16-byte aligned buffers");
+  if (r < 0) return fail(DRRT_ERR_RESOLUTION, "grid too large for one launch");
+  g_launches += r;
+  return check_launch("adam_step_multimem");
+}
+
 int drrt_adam_step(float *n, const float *grad, float *exp_avg, float *exp_avg_sq, int S0, int S1, int S2,
                    int step, float lr, float beta1, float beta2, float eps, float clamp_min,
                    unsigned flags, drrt_stream_t stream) {

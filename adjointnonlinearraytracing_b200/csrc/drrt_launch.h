@@ -162,6 +162,10 @@ int launch_adam_step_peers(float *const *n_replicas, const float *const *grad_re
                            float *m, float *v, int S0, int S1, int S2, int i0_begin, int i0_count, int step,
                            float lr, float beta1, float beta2, float eps, float clamp_min, bool zero_boundary,
                            bool clamp, cudaStream_t s);
+// the sharded step with the switch doing the gradient sum and the broadcast of the new slab (multicast addresses)
+int launch_adam_step_multimem(float *n_mc, const float *g_mc, const float *n_local, float *m, float *v, int S0, int S1,
+                              int S2, int i0_begin, int i0_count, int step, float lr, float beta1, float beta2, float eps,
+                              float clamp_min, bool zero_boundary, bool clamp, cudaStream_t s);
 int launch_upres_volume(const float *src, int s0, int s1, int s2, float *dst, int d0, int d1, int d2,
                         cudaStream_t s);
 

@@ -171,6 +171,59 @@ int launch_adam_step_peers(float *const *n_replicas, const float *const *grad_re
 }
 
 // ---------------------------------------------------------------------------
+// The same sharded step with the SWITCH doing the sum and the broadcast (NVLink SHARP): `g_mc` and `n_mc` are the
+// multicast addresses of the gradient grid and of the IOR grid (one virtual address bound to every rank's copy).  For each
+// float4 of its slab a rank issues ONE multimem.ld_reduce (the switch fetches the P private gradients and returns their
+// sum), applies boundary-zero + Adam + clamp with the local slab of the Adam state and its local copy of n, and issues ONE
+// multimem.st that lands the new value in all P replicas.  Per GPU the links carry the grid once out (its copy of the
+// gradient, pulled by the switch) and once in (the updated slabs) instead of 2 x (P-1)/P x in each direction for the
+// P2P kernel above or a ring.  Rows of S2 % 4 == 0 floats only (the caller falls back to the P2P kernel otherwise).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) adam_step_multimem_kernel(float *n_mc, const float *g_mc, const float *__restrict__ n_local,
+                                                                 float *__restrict__ m, float *__restrict__ v, int S0, int S1,
+                                                                 int S2, int i0_begin, int bpr, AdamP p) {
+  const int row = blockIdx.x / bpr;  // (i0 - i0_begin) * S1 + i1
+  const int i0 = row / S1 + i0_begin, i1 = row - (row / S1) * S1;
+  const int i2 = ((blockIdx.x - row * bpr) * blockDim.x + threadIdx.x) * 4;
+  if (i2 >= S2) return;
+  const bool row_boundary = p.zero_boundary && (i0 == 0 || i0 == S0 - 1 || i1 == 0 || i1 == S1 - 1);
+  const size_t local = (size_t) row * S2 + i2;
+  const size_t base = ((size_t) i0 * S1 + i1) * S2 + i2;
+  float4 gg;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(gg.x), "=f"(gg.y), "=f"(gg.z), "=f"(gg.w) : "l"(g_mc + base) : "memory");
+  float4 nn = *reinterpret_cast<const float4 *>(n_local + base);
+  float4 mm = *reinterpret_cast<float4 *>(m + local), vv = *reinterpret_cast<float4 *>(v + local);
+  if (row_boundary) gg = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.zero_boundary && i2 == 0) gg.x = 0.f;
+  if (p.zero_boundary && i2 + 3 == S2 - 1) gg.w = 0.f;
+  adam_one(nn.x, gg.x, mm.x, vv.x, p); adam_one(nn.y, gg.y, mm.y, vv.y, p);
+  adam_one(nn.z, gg.z, mm.z, vv.z, p); adam_one(nn.w, gg.w, mm.w, vv.w, p);
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+               :: "l"(n_mc + base), "f"(nn.x), "f"(nn.y), "f"(nn.z), "f"(nn.w) : "memory");
+  *reinterpret_cast<float4 *>(m + local) = mm;
+  *reinterpret_cast<float4 *>(v + local) = vv;
+}
+
+int launch_adam_step_multimem(float *n_mc, const float *g_mc, const float *n_local, float *m, float *v, int S0, int S1,
+                              int S2, int i0_begin, int i0_count, int step, float lr, float beta1, float beta2, float eps,
+                              float clamp_min, bool zero_boundary, bool clamp, cudaStream_t s) {
+  if ((int64_t) i0_count * S1 * S2 <= 0) return 0;
+  if (S2 % 4 || (((uintptr_t) n_mc | (uintptr_t) g_mc | (uintptr_t) n_local | (uintptr_t) m | (uintptr_t) v) & 15)) return -2;
+  AdamP p;
+  const double bc1 = 1.0 - pow((double) beta1, (double) step), bc2 = 1.0 - pow((double) beta2, (double) step);
+  p.lr_over_bc1 = (float) ((double) lr / bc1);
+  p.rsqrt_bc2 = (float) (1.0 / sqrt(bc2));
+  p.beta1 = beta1; p.beta2 = beta2; p.eps = eps; p.clamp_min = clamp_min;
+  p.zero_boundary = zero_boundary; p.clamp = clamp;
+  const int bpr = (S2 / 4 + 127) / 128;
+  const int64_t nblocks = (int64_t) i0_count * S1 * bpr;
+  if (nblocks > 0x7fffffffLL) return -1;
+  adam_step_multimem_kernel<<<(unsigned) nblocks, 128, 0, s>>>(n_mc, g_mc, n_local, m, v, S0, S1, S2, i0_begin, bpr, p);
+  return 1;
+}
+
+// ---------------------------------------------------------------------------
 // upres_volume (core/grid.py:318-330 -> Grid.GetLinear :227-273), evaluated like the
 // reference in float64 (core/optimizer.py:10 converts to double first):
 //   x_k = linspace(0, 1, d_k)[i_k];  norm = x / h, h = 1 / max(s_0 - 1, 1);

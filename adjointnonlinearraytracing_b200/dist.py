@@ -30,6 +30,18 @@ def shard_bounds(n: int, rank: int, world: int) -> Tuple[int, int]:
     return start, start + base + (1 if rank < rem else 0)
 
 
+def shard_cyclic(n: int, rank: int, world: int, block: int):
+    """Block-cyclic shard: rank r takes blocks r, r + world, r + 2 world, ... of `block` consecutive rays (the last block
+    may be short).  Returns a list of (start, end) ranges.  Contiguous blocks give every rank one REGION of the sensor,
+    and regions differ in cost (rays through the middle of the volume bend more and change cells on more axes: measured
+    5.73 ms for the slowest of 4 ranks against 5.15 ms on average on the 256^3 batch); cyclic blocks of whole sensor rows
+    give every rank the same mix while a warp still holds 32 neighbouring pixels."""
+    if world <= 0 or not (0 <= rank < world) or block <= 0:
+        raise ValueError("bad rank/world/block")
+    nblocks = (n + block - 1) // block
+    return [(b * block, min(n, (b + 1) * block)) for b in range(rank, nblocks, world)]
+
+
 def shard_rays(rank: int, world: int, *tensors):
     """Slice every (N, 3) / (N,) tensor to this rank's block."""
     n = tensors[0].shape[0]
@@ -303,6 +315,53 @@ class PeerShardedAdam:
             torch.cuda.synchronize(self.n.device)
             dist.barrier(group=self.ar.group)
             _capi.load().drrt_ipc_close_all()
+
+
+class SwitchShardedAdam:
+    """``PeerShardedAdam`` with the NVSwitch doing the gradient sum and the broadcast of the new slab
+    (``drrt_adam_step_multimem``): one ``multimem.ld_reduce`` and one ``multimem.st`` per float4 of this rank's slab.
+    Per GPU the links carry the grid once out (its gradient copy, pulled by the switch) and once in (the updated slabs).
+
+    ``n`` and ``grad`` must be buffers of ``switch.alloc()`` (a ``SwitchAllReduce``): create the grid with
+    ``n = switch.alloc(shape, device); n.copy_(n0)`` and pass ``out=grad`` to ``ops.backtrace``.  Same ordering contract
+    as ``PeerShardedAdam`` (two stream barriers, here the symmetric-memory ones).  Rows of ``n.shape[2] % 4 == 0``."""
+
+    def __init__(self, switch: "SwitchAllReduce", n: torch.Tensor, grad: torch.Tensor, lr: float, betas=(0.9, 0.999),
+                 eps: float = 1e-8, clamp_min: float = 1.0):
+        if grad.shape != n.shape or n.dim() != 3:
+            raise RuntimeError("Resolution doesn't match data")
+        if n.shape[2] % 4:
+            raise RuntimeError("SwitchShardedAdam: rows must hold a multiple of 4 floats (use PeerShardedAdam otherwise)")
+        en, eg = switch._handles.get(n.data_ptr()), switch._handles.get(grad.data_ptr())
+        if en is None or eg is None:
+            raise RuntimeError("SwitchShardedAdam: n and grad must be buffers of SwitchAllReduce.alloc()")
+        self.sw, self.n, self.grad = switch, n, grad
+        self.world, self.rank = switch.world, switch.rank
+        if n.shape[0] % self.world:
+            raise RuntimeError(f"SwitchShardedAdam: {n.shape[0]} planes do not split into {self.world} equal slabs")
+        self._hdl, self._n_mc, self._g_mc = eg[0], en[1], eg[1]
+        self.planes = n.shape[0] // self.world
+        self.i0 = self.rank * self.planes
+        self.lr, self.betas, self.eps, self.clamp_min = float(lr), tuple(betas), float(eps), float(clamp_min)
+        self.step_count = 0
+        slab_shape = (self.planes,) + tuple(n.shape[1:])
+        self.exp_avg = torch.zeros(slab_shape, device=n.device)
+        self.exp_avg_sq = torch.zeros(slab_shape, device=n.device)
+
+    def step(self) -> torch.Tensor:
+        n = self.n
+        self.step_count += 1
+        with torch.cuda.device(n.device):
+            stream = c_void_p(torch.cuda.current_stream(n.device).cuda_stream)
+            if self.world > 1:
+                self._hdl.barrier(channel=0)  # every rank's adjoint has finished writing its gradient copy
+            _capi.check(_capi.load().drrt_adam_step_multimem(
+                c_void_p(self._n_mc), c_void_p(self._g_mc), c_void_p(n.data_ptr()), c_void_p(self.exp_avg.data_ptr()),
+                c_void_p(self.exp_avg_sq.data_ptr()), int(n.shape[0]), int(n.shape[1]), int(n.shape[2]), self.i0,
+                self.planes, self.step_count, self.lr, self.betas[0], self.betas[1], self.eps, self.clamp_min, 0, stream))
+            if self.world > 1:
+                self._hdl.barrier(channel=1)  # every slab has landed in every replica
+        return n
 
 
 class ShardedTracer:

@@ -7,8 +7,8 @@
 One "step" = one forward trace + one adjoint backtrace (+ gradient all-reduce when N > 1) over one
 ray batch.  Workload (config.workload): BASELINE.json configs[3] "caustic design" AS WRITTEN: 256^3 IOR
 grid (Gaussian-bump field A of SURVEY.md section 8d), 2048^2 = 4 194 304 collimated rays IN TOTAL, ds = h/2,
-adjoint seeds dx = dv = 1 (reference src/test.cpp:142-144).  N > 1: the batch is sharded in contiguous blocks
-(dist.shard_bounds), i.e. STRONG scaling; the weak figure (4 M rays per rank) is measured too and reported
+adjoint seeds dx = dv = 1 (reference src/test.cpp:142-144).  N > 1: the batch's sensor rows are dealt out cyclically
+(dist.shard_cyclic), i.e. STRONG scaling; the weak figure (4 M rays per rank) is measured too and reported
 under `secondary.weak`.  Every N > 1 run checks the all-reduced gradient against a single-GPU gradient of
 the whole batch (`grad_check`) and reports the collective's own time.
 
@@ -405,7 +405,7 @@ def run_ours(args):
     import __graft_entry__ as ge
     ge.build()
     from adjointnonlinearraytracing_b200 import _capi, ops
-    from adjointnonlinearraytracing_b200.dist import GradAllReduce, shard_bounds
+    from adjointnonlinearraytracing_b200.dist import GradAllReduce, shard_cyclic
 
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -533,9 +533,12 @@ def run_ours(args):
         return t.tolist(), t.tolist()
 
     # ---- this rank's batch ---------------------------------------------------------
-    a, b = shard_bounds(n_total, rank, world) if strong else (0, n_total)
-    pos_pin = torch.from_numpy(np.ascontiguousarray(pos_h[a:b])).pin_memory()
-    vel_pin = torch.from_numpy(np.ascontiguousarray(vel_h[a:b])).pin_memory()
+    if strong and world > 1:  # sensor rows dealt out cyclically: every rank gets the same mix of cheap and expensive rays
+        sel = np.concatenate([np.arange(a, b) for a, b in shard_cyclic(n_total, rank, world, SENSOR)])
+    else:
+        sel = slice(0, n_total)
+    pos_pin = torch.from_numpy(np.ascontiguousarray(pos_h[sel])).pin_memory()
+    vel_pin = torch.from_numpy(np.ascontiguousarray(vel_h[sel])).pin_memory()
     n_rays = pos_pin.shape[0]
 
     m = measure(pos_pin, vel_pin, args.steps, args.warmup, True)
@@ -724,7 +727,7 @@ def run_ours(args):
             "config": {
                 "workload": workload_name(),
                 "rays_total": n_total * (1 if strong else world), "rays_per_gpu": n_rays, "grid": [NG, NG, NG],
-                "parallelism": (f"rays-dp{world} (contiguous blocks of the one batch) + private gradient grids + one gradient sum: {collective['used']}"
+                "parallelism": (f"rays-dp{world} (sensor rows of the one batch dealt out cyclically, dist.shard_cyclic) + private gradient grids + one gradient sum: {collective['used']}"
                                 if world > 1 else "single GPU"),
                 "l2": (f"no explicit flush: per-step working set (rays in/out {n_rays * 72 / 1e6:.0f} MB + grid {NG ** 3 * 4 / 1e6:.0f} MB + "
                        f"gradient {NG ** 3 * 4 / 1e6:.0f} MB) exceeds the 126 MB L2"

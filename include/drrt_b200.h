@@ -244,6 +244,14 @@ int drrt_adam_step_peers(float *const *n_replicas, const float *const *grad_repl
                          float *exp_avg_slab, float *exp_avg_sq_slab, int S0, int S1, int S2, int i0_begin,
                          int i0_count, int step, float lr, float beta1, float beta2, float eps, float clamp_min,
                          unsigned flags, drrt_stream_t stream);
+/* The same sharded step with the NVSwitch doing the gradient sum and the broadcast (NVLink SHARP): `n_multicast` /
+ * `grad_multicast` are the MULTICAST addresses of the IOR grid and of the gradient grid (one virtual address bound to
+ * every rank's copy; the caller creates the mappings, e.g. torch.distributed._symmetric_memory), `n_local` this rank's
+ * own copy of the grid.  One multimem.ld_reduce and one multimem.st per float4 of the slab; S2 % 4 == 0.  Ordering
+ * as for drrt_adam_step_peers (dist.SwitchShardedAdam). */
+int drrt_adam_step_multimem(float *n_multicast, const float *grad_multicast, const float *n_local, float *exp_avg_slab,
+                            float *exp_avg_sq_slab, int S0, int S1, int S2, int i0_begin, int i0_count, int step, float lr,
+                            float beta1, float beta2, float eps, float clamp_min, unsigned flags, drrt_stream_t stream);
 int drrt_upres_volume(const float *src, int s0, int s1, int s2, float *dst, int d0, int d1, int d2,
                       drrt_stream_t stream);
 

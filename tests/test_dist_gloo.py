@@ -132,3 +132,20 @@ def test_two_rank_sharded_adam_matches_single_process(tmp_path, oracle_mod):
     n0 = np.load(tmp_path / "n0.npy"); n1 = np.load(tmp_path / "n1.npy")
     assert np.array_equal(n0, n1)  # every rank holds the same updated grid
     assert np.array_equal(n0, n)   # and it is the single-process result
+
+
+def test_shard_cyclic_covers_every_ray_once():
+    from adjointnonlinearraytracing_b200.dist import shard_cyclic
+    for n, world, block in ((4194304, 8, 2048), (1000, 3, 64), (5, 4, 2), (7, 1, 3)):
+        seen = np.zeros(n, np.int32)
+        sizes = []
+        for r in range(world):
+            tot = 0
+            for a, b in shard_cyclic(n, r, world, block):
+                assert 0 <= a < b <= n and b - a <= block and a % block == 0
+                seen[a:b] += 1; tot += b - a
+            sizes.append(tot)
+        assert (seen == 1).all()
+        assert max(sizes) - min(sizes) <= block
+    with pytest.raises(ValueError):
+        shard_cyclic(10, 2, 2, 4)

@@ -387,3 +387,63 @@ def test_switch_allreduce_argument_checks(cuda_lib):
     assert lib.drrt_allreduce_multimem(buf, 16, 2, 2, None) == -1
     assert lib.drrt_allreduce_multimem(buf, 18, 0, 2, None) == -1
     assert lib.drrt_allreduce_multimem(ctypes.c_void_p(260), 16, 0, 2, None) == -1
+
+
+def _switch_adam_worker(rank, world, port, out_dir):
+    import os, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from adjointnonlinearraytracing_b200 import ops
+        from adjointnonlinearraytracing_b200.dist import SwitchAllReduce, SwitchShardedAdam
+        try:
+            sw = SwitchAllReduce()
+            shape = (8, 6, 16)
+            n = sw.alloc(shape, torch.device("cuda", rank)); g = sw.alloc(shape, torch.device("cuda", rank))
+        except Exception:  # noqa: BLE001
+            np.save(os.path.join(out_dir, f"sa{rank}.npy"), np.array([-1.0, 0]))
+            return
+        gen = torch.Generator(device="cuda").manual_seed(3)  # the same numbers on every rank
+        n0 = 1.0 + 0.2 * torch.rand(shape, device="cuda", generator=gen)
+        grads = [[torch.randn(shape, device="cuda", generator=gen) for _ in range(world)] for _ in range(3)]
+        n.copy_(n0)
+        opt = SwitchShardedAdam(sw, n, g, 1e-2)
+        ref = n0.clone(); m = torch.zeros_like(ref); v = torch.zeros_like(ref)
+        for it in range(3):
+            g.copy_(grads[it][rank])
+            opt.step()
+            total = grads[it][0].clone()
+            for r in range(1, world):
+                total += grads[it][r]
+            ops.adam_step_(ref, total, m, v, it + 1, 1e-2)
+        torch.cuda.synchronize()
+        lo, hi = opt.i0, opt.i0 + opt.planes
+        np.save(os.path.join(out_dir, f"sa{rank}.npy"),
+                np.array([float((n - ref).abs().max()), float((opt.exp_avg - m[lo:hi]).abs().max())]))
+        np.save(os.path.join(out_dir, f"san{rank}.npy"), n.cpu().numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(300)
+def test_switch_sharded_adam_two_gpus(cuda_lib, tmp_path):
+    """The sharded optimiser step with the switch summing the gradients and broadcasting the slab
+    (drrt_adam_step_multimem) against the whole-grid step on the summed gradient; every replica identical."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import socket
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+    mp.spawn(_switch_adam_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    for r in range(2):
+        e = np.load(tmp_path / f"sa{r}.npy")
+        if e[0] < 0:
+            pytest.skip("no multicast mapping on this fabric")
+        assert e[0] <= 1e-6 and e[1] <= 1e-6, (r, e)
+    assert np.array_equal(np.load(tmp_path / "san0.npy"), np.load(tmp_path / "san1.npy"))

@@ -66,6 +66,26 @@ if rank == 0:
     print(f"{res}^3, {world} ranks: one kernel over peer memory (two 4-byte barriers + P2P sum + Adam + P2P store) "
           f"{t_peer:.3f} ms; one barrier alone {t_bar:.3f} ms", flush=True)
 popt.close()
+# the switch does the sum and the broadcast: dist.SwitchShardedAdam (drrt_adam_step_multimem), checked against the peer kernel
+if world > 1:
+    try:
+        from adjointnonlinearraytracing_b200.dist import SwitchAllReduce, SwitchShardedAdam
+        sw = SwitchAllReduce()
+        n4 = sw.alloc(shape, torch.device("cuda", rank)); g4 = sw.alloc(shape, torch.device("cuda", rank))
+        n4.copy_(n); g4.copy_(grad)
+        sopt = SwitchShardedAdam(sw, n4, g4, 1e-3)
+        n5 = n.clone(); ref = PeerShardedAdam(n5, grad, 1e-3, allreduce=ar)
+        sopt.step(); ref.step(); torch.cuda.synchronize()
+        err = float((n4 - n5).abs().max())
+        t_sw = timeit(lambda: sopt.step())
+        t_swar = timeit(lambda: sw(g4))
+        if rank == 0:
+            print(f"{res}^3, {world} ranks: ONE kernel through the switch (2 barriers + multimem.ld_reduce + Adam + multimem.st) "
+                  f"{t_sw:.3f} ms; max |n - n_peer_kernel| after one step {err:.1e}; in-switch all-reduce alone {t_swar:.3f} ms", flush=True)
+        ref.close()
+    except Exception as e:  # noqa: BLE001
+        if rank == 0:
+            print("switch path unavailable:", repr(e)[:300], flush=True)
 if rank == 0:
     print(f"{res}^3, {world} ranks: all-reduce alone {t_ar:.3f} ms; all-reduce + whole-grid Adam {t_full:.3f} ms; "
           f"reduce-scatter + slab Adam + all-gather {t_sh:.3f} ms; Adam state per rank {2 * n.numel() * 4 / 2**20:.0f} -> "
