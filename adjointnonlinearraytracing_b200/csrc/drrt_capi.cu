@@ -126,6 +126,13 @@ int pair_of(unsigned flags, int64_t N) {
   return 0;
 }
 
+// Gather from a shared-memory copy of the grid (trace_kernel / backtrace_kernel <..., SM>): grids of up to 50 000 voxels
+// (200 KB; 36^3) and batches of at most 512 rays per SM -- beyond that the batch has the warps to hide the gather itself.
+int smem_grid_of(unsigned flags, int64_t G, int64_t N) {
+  if (flags & DRRT_NO_SMEM_GRID) return 0;
+  return G * 4 <= 200 * 1024 && N <= 148 * 512 ? 1 : 0;
+}
+
 int trace_common(int kind, const float *rif, const float *sdf, int W, int H, int D,
                  const float *pos, const float *vel, const float *aux0, const float *aux1,
                  int64_t N, int layout, float h, float ds, float *xt, float *vt,
@@ -154,6 +161,7 @@ int trace_common(int kind, const float *rif, const float *sdf, int W, int H, int
     CU_TRY(cudaMemsetAsync(a.tail_max_iters, 0, sizeof(int), s));
   }
   a.pair = pair_of(flags, N);
+  a.smem_grid = smem_grid_of(flags, (int64_t) W * H * D, N);
   a.one = 1.0f;
   g_launches += launch_trace(kind, arith_of(flags), a, s);
   rc = check_launch("trace");
@@ -214,6 +222,7 @@ int backtrace_common(bool sdf_kind, const float *rif, const float *sdf, int W, i
   // ~6 steps per cell on its branchy flush costs more than the atomics it saves (Luneburg yaml shape:
   // ds = h/4 7.2 vs 8.9 ms with / without, h/8 12.6 vs 11.1, h/32 39.3 vs 37.4;
   // profiles/r09_facecarry_vs_step.log), so it is chosen from h/ds unless a flag decides.
+  a.smem_grid = smem_grid_of(flags, G, N);
   a.face_carry = (flags & DRRT_NO_FACE_CARRY) ? 0 : (flags & DRRT_FACE_CARRY) ? 1 : (h < 6.0f * ds ? 1 : 0);
   unsigned long long *fixed = nullptr;
   unsigned *max_bits = nullptr;

@@ -212,14 +212,21 @@ __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
 
 // Corner values as x-adjacent pairs: V[j] = (v[2j], v[2j+1]) = (x0, x1) at
 // (y,z) = (0,0), (1,0), (0,1), (1,1).
+// SM: the grid pointer addresses a shared-memory copy of the whole grid (small grids, see trace_kernel): plain loads,
+// which the compiler turns into LDS; otherwise the non-coherent global path.
+template <bool SM>
+__device__ __forceinline__ float ldv(const float *p) { return SM ? *p : __ldg(p); }
+
+template <bool SM = false>
 __device__ __forceinline__ void load_corner_pairs(const GridP &g, const CellAddr &a, f32x2 V[4]) {
 #pragma unroll
-  for (int j = 0; j < 4; ++j) V[j] = pk2(__ldg(g.data + a.at(2 * j)), __ldg(g.data + a.at(2 * j + 1)));
+  for (int j = 0; j < 4; ++j) V[j] = pk2(ldv<SM>(g.data + a.at(2 * j)), ldv<SM>(g.data + a.at(2 * j + 1)));
 }
 
 // Address + gather of one cell.  Cells strictly inside the grid (all but the rays'
 // first and last steps) take the fast path: unit strides, four row pointers, the
 // x+1 neighbour as an immediate offset.
+template <bool SM = false>
 __device__ __forceinline__ CellAddr gather_cell(const GridP &g, int cx, int cy, int cz, f32x2 V[4]) {
   CellAddr a;
   const bool interior = ((unsigned) cx < (unsigned) (g.W - 1)) & ((unsigned) cy < (unsigned) (g.H - 1)) &
@@ -228,13 +235,13 @@ __device__ __forceinline__ CellAddr gather_cell(const GridP &g, int cx, int cy, 
     a.base = (cz * g.H + cy) * g.W + cx;
     a.dx = 1; a.dy = g.W; a.dz = g.H * g.W;
     const float *p00 = g.data + a.base, *p10 = p00 + a.dy, *p01 = p00 + a.dz, *p11 = p01 + a.dy;
-    V[0] = pk2(__ldg(p00), __ldg(p00 + 1));
-    V[1] = pk2(__ldg(p10), __ldg(p10 + 1));
-    V[2] = pk2(__ldg(p01), __ldg(p01 + 1));
-    V[3] = pk2(__ldg(p11), __ldg(p11 + 1));
+    V[0] = pk2(ldv<SM>(p00), ldv<SM>(p00 + 1));
+    V[1] = pk2(ldv<SM>(p10), ldv<SM>(p10 + 1));
+    V[2] = pk2(ldv<SM>(p01), ldv<SM>(p01 + 1));
+    V[3] = pk2(ldv<SM>(p11), ldv<SM>(p11 + 1));
   } else {
     a = corner_addr(g, cx, cy, cz);
-    load_corner_pairs(g, a, V);
+    load_corner_pairs<SM>(g, a, V);
   }
   return a;
 }

@@ -39,15 +39,16 @@ struct CellTag {
   __device__ __forceinline__ void set(const CellIdx &c) { fx = c.fx; fy = c.fy; fz = c.fz; }
 };
 
-template <int AR>
+// SM: the grid is a shared-memory copy (small grids)
+template <int AR, bool SM = false>
 struct CellCache;
 
-template <>
-struct CellCache<A_REF> : CellTag {
+template <bool SM>
+struct CellCache<A_REF, SM> : CellTag {
   f32x2 V[4];  // x-adjacent corner pairs
   __device__ __forceinline__ CellAddr refill(const GridP &g, const CellIdx &c) {
     set(c);
-    return gather_cell(g, c.cx(), c.cy(), c.cz(), V);
+    return gather_cell<SM>(g, c.cx(), c.cy(), c.cz(), V);
   }
   __device__ __forceinline__ void eval(const GridP &g, const CellIdx &c, float &n, f3 &nx, f3 *hm) const {
     eval_grad_ref_x2(g, V, c.wx, c.wy, c.wz, n, nx);
@@ -58,13 +59,13 @@ struct CellCache<A_REF> : CellTag {
   }
 };
 
-template <>
-struct CellCache<A_FAST> : CellTag {
+template <bool SM>
+struct CellCache<A_FAST, SM> : CellTag {
   CellPoly p;
   __device__ __forceinline__ CellAddr refill(const GridP &g, const CellIdx &c) {
     set(c);
     f32x2 V[4];
-    CellAddr a = gather_cell(g, c.cx(), c.cy(), c.cz(), V);
+    CellAddr a = gather_cell<SM>(g, c.cx(), c.cy(), c.cz(), V);
     const float v[8] = {lo2(V[0]), hi2(V[0]), lo2(V[1]), hi2(V[1]), lo2(V[2]), hi2(V[2]), lo2(V[3]), hi2(V[3])};
     p = make_poly(v);
     return a;
@@ -81,8 +82,8 @@ struct CellCache<A_FAST> : CellTag {
   }
 };
 
-template <>
-struct CellCache<A_EXACT> : CellTag {
+template <bool SM>
+struct CellCache<A_EXACT, SM> : CellTag {
   f32x2 V[4];  // x-adjacent corner pairs
   // mixed second differences in the reference's association order
   // (src/volume.cpp:79-90; they cancel to ~1e-4 of the voxel values, so the order
@@ -91,7 +92,7 @@ struct CellCache<A_EXACT> : CellTag {
   float hxy0, hxys, hxz0, hxzs, hyz0, hyzs;
   __device__ __forceinline__ CellAddr refill(const GridP &g, const CellIdx &c) {
     set(c);
-    CellAddr a = gather_cell(g, c.cx(), c.cy(), c.cz(), V);
+    CellAddr a = gather_cell<SM>(g, c.cx(), c.cy(), c.cz(), V);
     const float r2 = mul_(g.rcp_h, g.rcp_h);
     const float v000 = lo2(V[0]), v100 = hi2(V[0]), v010 = lo2(V[1]), v110 = hi2(V[1]);
     const float v001 = lo2(V[2]), v101 = hi2(V[2]), v011 = lo2(V[3]), v111 = hi2(V[3]);
@@ -114,8 +115,8 @@ struct CellCache<A_EXACT> : CellTag {
 };
 
 // Trilinear value only (sdf lookups), src/volume.cpp:162-163 under the caller's mask.
-template <int AR>
-__device__ __forceinline__ float eval_value(const GridP &g, CellCache<AR> &cc, f3 x) {
+template <int AR, class CC = CellCache<AR>>
+__device__ __forceinline__ float eval_value(const GridP &g, CC &cc, f3 x) {
   CellIdx c = cell_of(g, x);
   if (cc.differs(c)) cc.refill(g, c);
   float n; f3 nx;
@@ -132,15 +133,33 @@ __device__ __forceinline__ float dist2_ref(f3 x, f3 t) {
 // Forward: Tracer::trace (src/tracer.cpp:35-100), trace_plane (:102-172),
 // trace_target (:174-242, per-ray part), trace_sdf (:244-310).
 // ---------------------------------------------------------------------------
-template <int KIND, int AR>
-__global__ void __launch_bounds__(kTraceThreads, KIND == K_PLAIN ? kTraceMinBlocks : 8) trace_kernel(TraceArgs a) {
+// Small grids (SM): a batch of <= ~10^5 rays leaves 3-4 warps per scheduler, too few to hide the L2 round trip of the
+// gather that follows every cell change -- it is 28 % of the forward kernel's stall samples at 32^3 / 256^2
+// (profiles/r12_luneburg32_full.txt).  When the whole grid fits a CTA's shared memory (<= 50 000 voxels) the kernel
+// runs as one CTA of up to 512 rays per SM, copies the grid in once and gathers from shared memory.
+constexpr int kSmemGridThreads = 512;
+extern __shared__ float s_grid[];
+
+template <bool SM>
+__device__ __forceinline__ GridP grid_in_smem(GridP g) {
+  if (SM) {
+    const int G = g.W * g.H * g.D;
+    for (int i = threadIdx.x; i < G; i += blockDim.x) s_grid[i] = __ldg(g.data + i);
+    __syncthreads();
+    g.data = s_grid;
+  }
+  return g;
+}
+
+template <int KIND, int AR, bool SM = false>
+__global__ void __launch_bounds__(SM ? kSmemGridThreads : kTraceThreads, SM ? 1 : KIND == K_PLAIN ? kTraceMinBlocks : 8) trace_kernel(TraceArgs a) {
   constexpr bool REF = AR != A_FAST;
   const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
   const bool valid = r < a.N;
   int steps = 0;  // per ray < max_steps < 2^31
   int not_exited = 0;
+  const GridP g = grid_in_smem<SM>(a.grid);
   if (valid) {
-    const GridP g = a.grid;
     const float ds = a.ds;
     f3 x = ld3(a.pos, r, a.N, a.layout), v = ld3(a.vel, r, a.N, a.layout);
     f3 xt = x, vt = v;
@@ -150,7 +169,7 @@ __global__ void __launch_bounds__(kTraceThreads, KIND == K_PLAIN ? kTraceMinBloc
     if (KIND == K_TARGET) { aux0 = ld3(a.aux0, r, a.N, a.layout); best = dist2_ref(x, aux0); }
     bool inside = inbounds(g, x);  // :61
     bool esc = false, crossed = false;
-    CellCache<AR> cc;
+    CellCache<AR, SM> cc;
     CellCache<AR> sc;  // sdf grid (K_SDF only)
     cc.reset(); sc.reset();
     GridP sg = g;
@@ -688,8 +707,8 @@ __global__ void __launch_bounds__(256) estimate_interleave_kernel(GridP g, const
 // dL/dvel = mu + (k - 1) ds lambda, with k the number of straight steps between the
 // launch position and the last processed sample (k = 0 when `pos0` is not given, which
 // is exact for rays launched on the first in-bounds sample).
-template <bool SDF, int AR, class Accum, bool AGG, bool RG = false>
-__global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : AGG ? kAdjMinBlocks - 1 : kAdjMinBlocks) backtrace_kernel(AdjArgs a, Accum out_in) {
+template <bool SDF, int AR, class Accum, bool AGG, bool RG = false, bool SM = false>
+__global__ void __launch_bounds__(SM ? kSmemGridThreads : kAdjThreads, SM ? 1 : (SDF || AR == A_REF || RG) ? 5 : AGG ? kAdjMinBlocks - 1 : kAdjMinBlocks) backtrace_kernel(AdjArgs a, Accum out_in) {
   constexpr bool REF = AR == A_REF;     // literal 16-atomic splat and lambda/mu order
   constexpr bool TRAJ_REF = AR != A_FAST;
   Accum out = out_in;
@@ -704,11 +723,11 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : 
   }
   const bool valid = r < a.N;
   int steps = 0;  // per ray < max_steps < 2^31
-  const GridP g = a.grid;
+  const GridP g = grid_in_smem<SM>(a.grid);
   const float ds = a.ds;
   f3 x = {0, 0, 0}, v = {0, 0, 0}, la = {0, 0, 0}, mu = {0, 0, 0};
   bool active = false;
-  CellCache<AR> cc;
+  CellCache<AR, SM> cc;
   CellCache<AR> sc;
   cc.reset(); sc.reset();
   GridP sg = g;
@@ -872,6 +891,13 @@ __global__ void __launch_bounds__(kAdjThreads, (SDF || AR == A_REF || RG) ? 5 : 
 // ---------------------------------------------------------------------------
 static inline unsigned blocks_for(int64_t n, int threads) { return (unsigned) ((n + threads - 1) / threads); }
 
+// shared-memory grid variants: rays spread over the 148 SMs, one CTA each
+constexpr int kSmemGridBytes = 200 * 1024;
+static inline int smem_grid_threads(int64_t n) {
+  int64_t t = ((n + 147) / 148 + 31) / 32 * 32;
+  return (int) (t < 64 ? 64 : t > kSmemGridThreads ? kSmemGridThreads : t);
+}
+
 template <int KIND>
 static void launch_trace_kind(int arith, const TraceArgs &a, cudaStream_t s) {
   const int nt = kTraceThreads;  // 32 / 64 / 128 threads per CTA time the same, also below one wave (profiles/r09_cta_size.log)
@@ -879,6 +905,17 @@ static void launch_trace_kind(int arith, const TraceArgs &a, cudaStream_t s) {
   // the forward pass is all trajectory: A_EXACT and A_REF are the same kernel
   if (KIND == K_PLAIN && arith != A_FAST && a.pair) {
     trace_pair_kernel<<<blocks_for(((a.N + 63) / 64) * 32, nt), nt, 0, s>>>(a);
+    return;
+  }
+  if (KIND == K_PLAIN && arith != A_FAST && a.smem_grid) {  // small grid, small batch: one CTA per SM, grid in shared memory
+    const int t = smem_grid_threads(a.N);
+    const size_t bytes = sizeof(float) * (size_t) a.grid.W * a.grid.H * a.grid.D;
+    static const bool optin = [] {
+      cudaFuncSetAttribute(trace_kernel<K_PLAIN, A_REF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemGridBytes);
+      return true;
+    }();
+    (void) optin;
+    trace_kernel<K_PLAIN, A_REF, true><<<blocks_for(a.N, t), t, bytes, s>>>(a);
     return;
   }
   if (arith == A_FAST) trace_kernel<KIND, A_FAST><<<nb, nt, 0, s>>>(a);
@@ -918,6 +955,18 @@ static void launch_backtrace_acc(int arith, const AdjArgs &a, Accum acc, cudaStr
     if (arith == A_REF) backtrace_kernel<SDF, A_REF, Accum, false, true><<<nb, nt, 0, s>>>(a, acc);
     else if (arith == A_FAST) backtrace_kernel<SDF, A_FAST, Accum, false, true><<<nb, nt, 0, s>>>(a, acc);
     else backtrace_kernel<SDF, A_EXACT, Accum, false, true><<<nb, nt, 0, s>>>(a, acc);
+    return;
+  }
+  if (!SDF && !AGG && arith == A_EXACT && a.smem_grid && !a.interleave_log2) {  // see trace_kernel<..., SM>
+    const int t = smem_grid_threads(a.N);
+    const size_t bytes = sizeof(float) * (size_t) a.grid.W * a.grid.H * a.grid.D;
+    static const bool optin = [] {
+      cudaFuncSetAttribute(backtrace_kernel<false, A_EXACT, Accum, false, false, true>,
+                           cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemGridBytes);
+      return true;
+    }();
+    (void) optin;
+    backtrace_kernel<false, A_EXACT, Accum, false, false, true><<<blocks_for(a.N, t), t, bytes, s>>>(a, acc);
     return;
   }
   if (arith == A_REF) backtrace_kernel<SDF, A_REF, Accum, false><<<nb, nt, 0, s>>>(a, acc);

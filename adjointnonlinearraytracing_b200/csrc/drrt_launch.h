@@ -51,6 +51,7 @@ struct TraceArgs {
   float *tail_x, *tail_v;
   int *tail_iters, *tail_max_iters;
   int pair;   // trace only: two rays per thread (trace_pair_kernel)
+  int smem_grid;  // small grid + small batch: gather from a shared-memory copy of the grid (one CTA per SM)
   float one;  // 1.0f, opaque to the compiler (PairK)
 };
 
@@ -64,6 +65,7 @@ struct AdjArgs {
   int max_steps;
   int agg_policy;  // warp aggregation: 0 adaptive, 1 off, 2/4/8/32 fixed maximum run length
   int agg_t8, agg_twarp;  // adaptive: lanes per cell from which runs of 8 / the whole warp are summed
+  int smem_grid;   // small grid + small batch: gather from a shared-memory copy of the grid (one CTA per SM)
   int face_carry;  // keep the accumulators of the face shared with the next cell in registers
   int replicas;    // > 1: CTA b adds into gradient copy b % replicas (copy 0 = grad, the others in `replica_base`)
   float *replica_base;
