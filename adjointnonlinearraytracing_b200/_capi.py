@@ -28,7 +28,7 @@ DRRT_NO_REPLICAS = 1 << 19
 DRRT_FACE_CARRY = 1 << 24
 DRRT_PAIR_RAYS = 1 << 25
 DRRT_NO_PAIR_RAYS = 1 << 26
-DRRT_NO_SMEM_GRID = 1 << 27
+DRRT_SMEM_GRID = 1 << 27
 DRRT_AGG_RUN_WARP = 15 << 8
 
 

@@ -127,9 +127,12 @@ int pair_of(unsigned flags, int64_t N) {
 }
 
 // Gather from a shared-memory copy of the grid (trace_kernel / backtrace_kernel <..., SM>): grids of up to 50 000 voxels
-// (200 KB; 36^3) and batches of at most 512 rays per SM -- beyond that the batch has the warps to hide the gather itself.
+// (200 KB; 36^3) and batches of at most 512 rays per SM.  OPT-IN (DRRT_SMEM_GRID): measured slower than the default on
+// the 32^3 / 256^2 configuration (adjoint 0.167 vs 0.153 ms on the lens field, 0.126 vs 0.110 ms on the bump field,
+// forward 0.084 vs 0.073 ms; profiles/r12_smem_grid_rejected.log) -- 148 CTAs x 128 KB of grid copy and one 448-thread CTA
+// per SM at 90 registers cost more than the L2 round trips they remove.
 int smem_grid_of(unsigned flags, int64_t G, int64_t N) {
-  if (flags & DRRT_NO_SMEM_GRID) return 0;
+  if (!(flags & DRRT_SMEM_GRID)) return 0;
   return G * 4 <= 200 * 1024 && N <= 148 * 512 ? 1 : 0;
 }
 

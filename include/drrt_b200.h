@@ -101,9 +101,10 @@ enum {
    * float32 operation of the reference formulas issues as packed FP32 (FMUL2 / FFMA2, one instruction
    * per two rays; results bit-identical to one ray per thread); DRRT_NO_PAIR_RAYS forces one ray per
    * thread.  Neither bit: the library's choice ("Ray pairs"). */
-  /* A/B switch: do NOT use the shared-memory-grid kernels (drrt_trace / drrt_backtrace on grids of up to 50 000 voxels
-   * with at most 512 rays per SM gather from a per-CTA shared-memory copy of the grid; results identical). */
-  DRRT_NO_SMEM_GRID = 1u << 27,
+  /* Opt-in: drrt_trace / drrt_backtrace on grids of up to 50 000 voxels with at most 512 rays per SM gather from a
+   * per-CTA shared-memory copy of the grid (results identical; measured SLOWER than the default on the 32^3 / 256^2
+   * configuration, profiles/r12_smem_grid_rejected.log, hence not the default). */
+  DRRT_SMEM_GRID = 1u << 27,
   DRRT_PAIR_RAYS = 1u << 25,
   DRRT_NO_PAIR_RAYS = 1u << 26,
   /* Adjoint only: accumulate the gradient in 64-bit fixed point so the result is

@@ -275,3 +275,26 @@ def test_private_gradient_copies_only_change_the_summation_order(field, cuda_lib
     b = ops.backtrace(rif, xt[few].contiguous(), vt[few].contiguous(), dx[few].contiguous(), dv[few].contiguous(), h, ds,
                       flags=DET)
     assert rel_l2(a.cpu().numpy(), b.cpu().numpy()) <= 1e-5
+
+
+@pytest.mark.gpu
+def test_smem_grid_variant_is_identical(cuda_lib):
+    """DRRT_SMEM_GRID (opt-in: gather from a per-CTA shared-memory copy of a small grid, one CTA per SM): bit-identical
+    trajectory, gradient within atomic-order noise of the default kernels (32^3, rays from outside and ragged count)."""
+    from adjointnonlinearraytracing_b200 import _capi, ops, scenes as sc
+    ng = 32
+    rif = torch.from_numpy(sc.field_luneburg(ng)).cuda()
+    h = float(sc.grid_spacing(ng)); ds = h / 2
+    pos, vel = sc.rays_cone(61, spread=0.1, backoff=2.37 * ds)
+    pos, vel = torch.from_numpy(pos).cuda(), torch.from_numpy(vel).cuda()
+    st0, st1 = ops.new_stats("cuda"), ops.new_stats("cuda")
+    x0, v0 = ops.trace(rif, pos, vel, h, ds, stats=st0)
+    x1, v1 = ops.trace(rif, pos, vel, h, ds, flags=_capi.DRRT_SMEM_GRID, stats=st1)
+    assert torch.equal(x0, x1) and torch.equal(v0, v1) and torch.equal(st0, st1)
+    dx, dv = (torch.from_numpy(a).cuda() for a in sc.seeds_normal(pos.shape[0]))
+    g0 = ops.backtrace(rif, x0, v0, dx, dv, h, ds)
+    g1 = ops.backtrace(rif, x0, v0, dx, dv, h, ds, flags=_capi.DRRT_SMEM_GRID)
+    assert rel_l2(g1.cpu().numpy(), g0.cpu().numpy()) <= 1e-5
+    d0 = ops.backtrace(rif, x0, v0, dx, dv, h, ds, flags=DET)
+    d1 = ops.backtrace(rif, x0, v0, dx, dv, h, ds, flags=DET | _capi.DRRT_SMEM_GRID)
+    assert torch.equal(d0, d1)
