@@ -46,6 +46,7 @@ def DRRT_INTERLEAVE(n: int) -> int:
 DRRT_UNIQUE_ID_BYTES = 128
 DRRT_IPC_HANDLE_BYTES = 64
 DRRT_MAX_PEERS = 16
+DRRT_NOALLOC_MAX_VOXELS = 2146689  # 129^3: largest grid of drrt_backtrace_noalloc
 
 # every symbol include/drrt_b200.h declares (checked by tests/test_capi_symbols.py)
 _F, _I, _L, _U, _P = c_float, c_int, c_int64, c_uint, c_void_p
@@ -60,6 +61,7 @@ PROTOTYPES = {
     "drrt_trace_cable": (c_int, [_P, _I, _F, _F, _P, _P, _P, _L, _I, _F, _P, _P, _P, _P, _U, _P]),
     "drrt_backtrace_scratch_bytes": (c_size_t, [_L, _U]),
     "drrt_backtrace": (c_int, [_P, _I, _I, _I, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, c_size_t, _P, _U, _P]),
+    "drrt_backtrace_noalloc": (c_int, [_P, _I, _I, _I, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, _U, _P]),
     "drrt_backtrace_sdf": (c_int, [_P, _P, _I, _I, _I, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, c_size_t, _P, _U, _P]),
     "drrt_backtrace_cable": (c_int, [_P, _I, _F, _F, _P, _P, _P, _P, _L, _I, _F, _P, _P, c_size_t, _P, _U, _P]),
     "drrt_backtrace_rays": (c_int, [_P, _P, _I, _I, _I, _P, _P, _P, _P, _P, _L, _I, _F, _F, _P, _P, _P, _P, c_size_t, _P, _U, _P]),

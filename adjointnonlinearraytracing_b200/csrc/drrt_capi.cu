@@ -656,4 +656,56 @@ int drrt_allreduce_multimem(float *multicast_grad, size_t count, int rank, int n
   return check_launch("allreduce_multimem");
 }
 
+// ---------------------------------------------------------------------------
+// drrt_backtrace_noalloc: drrt_backtrace for callers that cannot allocate (code under CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The scratch that drrt_backtrace takes from its caller (the int64 grid of DRRT_DETERMINISTIC, or the private gradient
+// copies of small grids) lives in a file-scope device array of a fixed, modest size: every GPU that loads the library
+// holds it (17.2 MB) until the process exits.  `g_noalloc_scratch` is a HOST-side stand-in in host code, not a device
+// address: its device address is resolved once per device with cudaGetSymbolAddress (with that device current) and that
+// pointer is what the kernels get.  Every call shares the array and finds the previous call's contents in it: the part
+// a call uses is cleared (cudaMemsetAsync on `stream`) before its kernels run, and calls that overlap on the GPU
+// (different streams, no ordering between them) race.
+// ---------------------------------------------------------------------------
+namespace {
+constexpr size_t kNoAllocScratchBytes = sizeof(unsigned long long) * (size_t) DRRT_NOALLOC_MAX_VOXELS + 256;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+constexpr int kNoAllocMaxDevices = 64;
+std::atomic<void *> g_noalloc_ptr[kNoAllocMaxDevices];
+
+// Device address of the scratch array on the CURRENT device (resolved once per device).
+int noalloc_scratch(void **out) {
+  int dev = -1;
+  CU_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return fail(DRRT_ERR_INVALID_ARGUMENT, "drrt_backtrace_noalloc: device index out of range");
+  void *p = g_noalloc_ptr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p)
+      return fail(DRRT_ERR_CUDA, "drrt_backtrace_noalloc: cudaGetSymbolAddress(scratch): %s", cudaGetErrorString(e));
+    g_noalloc_ptr[dev].store(p, std::memory_order_release);  // the same address whichever thread resolves it
+  }
+  *out = p;
+  return DRRT_OK;
+}
+}  // namespace
+
+int drrt_backtrace_noalloc(const float *rif, int W, int H, int D, const float *xt, const float *vt, const float *dx,
+                           const float *dv, int64_t N, int layout, float h, float ds, float *grad, int64_t *stats,
+                           unsigned flags, drrt_stream_t stream) {
+  if (W <= 0 || H <= 0 || D <= 0) return fail(DRRT_ERR_RESOLUTION, "volume: invalid resolution!");
+  const int64_t G = (int64_t) W * H * D;
+  if (G > (int64_t) DRRT_NOALLOC_MAX_VOXELS)
+    return fail(DRRT_ERR_INVALID_ARGUMENT,
+                "drrt_backtrace_noalloc: a grid of %lld voxels exceeds the built-in scratch (DRRT_NOALLOC_MAX_VOXELS = %d); "
+                "use drrt_backtrace with a caller-owned scratch buffer", (long long) G, (int) DRRT_NOALLOC_MAX_VOXELS);
+  void *scratch = nullptr;
+  int rc = noalloc_scratch(&scratch);
+  if (rc) return rc;
+  // the ray interleave's device-side estimate takes a stream-ordered allocation: never on this path
+  flags = (flags & ~(DRRT_AUTO_INTERLEAVE | (0x3fu << 12))) | DRRT_NO_INTERLEAVE;
+  return backtrace_common(false, rif, nullptr, W, H, D, xt, vt, dx, dv, N, layout, h, ds, grad, scratch,
+                          kNoAllocScratchBytes, stats, flags, (cudaStream_t) stream);
+}
+
 }  // extern "C"

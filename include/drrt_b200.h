@@ -185,6 +185,27 @@ int drrt_backtrace_cable(const float *rif, int res, float radius, float length, 
                          float ds, float *grad, void *scratch, size_t scratch_bytes, int64_t *stats, unsigned flags,
                          drrt_stream_t stream);
 
+/* drrt_backtrace_noalloc: NO counterpart in the reference -- added for callers
+ * that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * drrt_backtrace without the scratch argument: the scratch (the int64 grid of DRRT_DETERMINISTIC, else the private
+ * gradient copies of small grids, as many as fit) is a static device array inside the library, so the call makes no
+ * cudaMalloc / cudaFree / cudaMallocAsync and uses no allocating library routine.  Limits and rules:
+ *   - grids of at most DRRT_NOALLOC_MAX_VOXELS voxels (129^3); larger grids are refused with
+ *     DRRT_ERR_INVALID_ARGUMENT (use drrt_backtrace with your own scratch);
+ *   - every GPU that loads the library holds the array (8 * DRRT_NOALLOC_MAX_VOXELS + 256 bytes = 17.2 MB) until exit;
+ *   - all calls share the array, which keeps the last call's contents: each call clears the part it uses on `stream`
+ *     before its kernels; calls that OVERLAP on the GPU (different streams with no ordering between them) race;
+ *   - the ray interleave is off on this path (DRRT_INTERLEAVE / DRRT_AUTO_INTERLEAVE are ignored: its estimate
+ *     allocates); results equal drrt_backtrace's with the same flags | DRRT_NO_INTERLEAVE (bit-identical in
+ *     deterministic mode, atomic-order noise otherwise);
+ *   - the first call on a device resolves the array's device address (cudaGetSymbolAddress; with lazy module loading the
+ *     driver loads the module then): make one call per device before starting a graph capture.
+ * Inputs and outputs stay the caller's, as for drrt_backtrace. */
+#define DRRT_NOALLOC_MAX_VOXELS 2146689
+int drrt_backtrace_noalloc(const float *rif, int W, int H, int D, const float *xt, const float *vt, const float *dx,
+                           const float *dv, int64_t N, int layout, float h, float ds, float *grad, int64_t *stats,
+                           unsigned flags, drrt_stream_t stream);
+
 /* drrt_backtrace_rays <- the ray-state half of ADTracerC.backward / ADSDFTracerC.backward
  * (reference core/tracer.py:53-60, :247-291: enoki.gradient(ctx.x), enoki.gradient(ctx.v)):
  * the same adjoint pass as drrt_backtrace (sdf == NULL) / drrt_backtrace_sdf, which in
