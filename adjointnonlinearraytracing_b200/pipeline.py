@@ -42,7 +42,12 @@ class HostStepPipeline:
 
     def __init__(self, rif: torch.Tensor, h: float, ds: float, n_rays: int, flags: int = 0,
                  allreduce: Optional[Callable[[torch.Tensor], torch.Tensor]] = None,
-                 seed_fn: Optional[Callable[[torch.Tensor, torch.Tensor], Tuple[torch.Tensor, torch.Tensor]]] = None):
+                 seed_fn: Optional[Callable[[torch.Tensor, torch.Tensor], Tuple[torch.Tensor, torch.Tensor]]] = None,
+                 host_planes: Optional[Tuple[int, int]] = None):
+        """``host_planes = (i0, count)``: copy only planes ``[i0, i0 + count)`` of the gradient grid to the host.  After
+        the all-reduce every rank holds the SAME summed gradient, so with one slab per rank (``dist.shard_bounds`` over
+        ``rif.shape[0]``) the job as a whole still lands the full gradient in host memory every step while each rank's
+        PCIe link carries 1/world of it; ``result()`` then returns that slab."""
         if not rif.is_cuda:
             raise RuntimeError("rif must be a CUDA tensor (there is no CPU path)")
         self.rif, self.h, self.ds, self.flags = rif, float(h), float(ds), int(flags)
@@ -56,7 +61,11 @@ class HostStepPipeline:
         alloc = getattr(allreduce, "alloc", None)  # a collective may need the gradient grid in its own buffers
         self.grad = [alloc(rif.shape, dev) if alloc is not None else torch.empty_like(rif) for _ in range(D)]
         self.stats = [ops.new_stats(dev) for _ in range(D)]
-        self.grad_host = [torch.empty(rif.shape, dtype=torch.float32).pin_memory() for _ in range(D)]
+        self.host_planes = (0, int(rif.shape[0])) if host_planes is None else (int(host_planes[0]), int(host_planes[1]))
+        if not (0 <= self.host_planes[0] and self.host_planes[0] + self.host_planes[1] <= rif.shape[0]):
+            raise RuntimeError("host_planes: slab outside the grid")
+        hshape = (self.host_planes[1],) + tuple(rif.shape[1:])
+        self.grad_host = [torch.empty(hshape, dtype=torch.float32).pin_memory() for _ in range(D)]
         self.stats_host = [torch.empty(2, dtype=torch.int64).pin_memory() for _ in range(D)]
         self.ones = torch.ones(n_rays, 3, device=dev) if seed_fn is None else None
         self.ev_in = [torch.cuda.Event() for _ in range(D)]
@@ -64,7 +73,7 @@ class HostStepPipeline:
         self.ev_out = [torch.cuda.Event() for _ in range(D)]
         self.k = 0
         self.h2d_bytes = 2 * n_rays * 3 * 4
-        self.d2h_bytes = rif.numel() * 4 + 16
+        self.d2h_bytes = self.grad_host[0].numel() * 4 + 16
 
     def submit(self, pos_host: torch.Tensor, vel_host: torch.Tensor) -> int:
         k, b = self.k, self.k % self.DEPTH
@@ -90,7 +99,8 @@ class HostStepPipeline:
         # copy-out
         with torch.cuda.stream(self.s_out):
             self.s_out.wait_event(self.ev_compute[b])
-            self.grad_host[b].copy_(self.grad[b], non_blocking=True)
+            i0, cnt = self.host_planes
+            self.grad_host[b].copy_(self.grad[b][i0:i0 + cnt], non_blocking=True)
             self.stats_host[b].copy_(self.stats[b], non_blocking=True)
             self.ev_out[b].record(self.s_out)
         # keep xt/vt alive until the kernels have consumed them (caching allocator is stream-aware

@@ -616,7 +616,13 @@ def run_ours(args):
     # the same step through the package's streaming API (pipeline.HostStepPipeline): copies of
     # batch k+1 / gradient k-1 overlap the kernels of batch k; every step's gradient is read on the host
     from adjointnonlinearraytracing_b200.pipeline import HostStepPipeline
-    pipe = HostStepPipeline(rif, h, ds, n_rays, flags=flags, allreduce=allreduce)
+    # N > 1: every rank holds the same summed gradient after the collective; each rank lands ITS slab of planes in host
+    # memory, so the job as a whole reads the full gradient grid on the host every step (d2h bytes summed over ranks =
+    # one grid + the counters) instead of N identical copies of it
+    from adjointnonlinearraytracing_b200.dist import shard_bounds
+    pa, pb = shard_bounds(NG, rank, world)
+    pipe = HostStepPipeline(rif, h, ds, n_rays, flags=flags, allreduce=allreduce,
+                            host_planes=(pa, pb - pa) if world > 1 else None)
     for _ in range(3):
         pipe.submit(pos_pin, vel_pin)
     pipe.drain()
@@ -636,7 +642,7 @@ def run_ours(args):
     e2e_ms = e0.elapsed_time(e1)
     assert checksum == args.steps * (s_f + s_b), (checksum, s_f, s_b)
     h2d = pos_pin.numel() * 4 + vel_pin.numel() * 4
-    d2h = grad_pin.numel() * 4 + stat_pin.numel() * 8
+    d2h = pipe.d2h_bytes
     del pipe
 
     # ---- reduce over ranks: max time, sum of work ----------------------------------
@@ -740,7 +746,7 @@ def run_ours(args):
             "roofline": roof,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(sm[7]), "d2h_bytes_per_step": int(sm[8]),
                     "ms_per_step": e2e_ms / args.steps,
-                    "path": "pipeline.HostStepPipeline: pinned host rays -> H2D -> ops.trace -> ops.backtrace -> allreduce -> D2H gradient grid + counters into pinned memory, read on the host every step; depth-2 double buffering on copy-in / compute / copy-out streams; bytes are the sum over ranks",
+                    "path": "pipeline.HostStepPipeline: pinned host rays -> H2D -> ops.trace -> ops.backtrace -> gradient sum -> D2H gradient grid + counters into pinned memory, read on the host every step; depth-2 double buffering on copy-in / compute / copy-out streams; bytes are the sum over ranks (N > 1: each rank lands its slab of the summed gradient, the job one full grid per step; serial_ms_per_step copies the whole grid on every rank)",
                     "serial_ms_per_step": e2e_serial_ms / args.steps},
             "gpu_launches": int(sm[9]), "clocks": m["clocks"],
             "secondary": {"fast_arith_ms_per_step": fast_ms, "fast_arith_ray_steps_per_s": (s_f + s_b) / (fast_ms * 1e-3),

@@ -39,6 +39,29 @@ def test_host_pipeline_matches_direct_calls(cuda_lib):
         assert torch.equal(got[k][1], stats.cpu()), k
 
 
+def test_host_pipeline_slab_copy(cuda_lib):
+    """host_planes: only the given planes of the gradient grid travel to the host (one slab per rank after the
+    all-reduce); they equal the same planes of the full result, and d2h_bytes counts the slab."""
+    from adjointnonlinearraytracing_b200 import ops, scenes as sc
+    from adjointnonlinearraytracing_b200.pipeline import HostStepPipeline
+    ng, s = 33, 48
+    rif = torch.from_numpy(sc.field_noise(ng)).cuda()
+    h = float(sc.grid_spacing(ng)); ds = h / 2
+    pos, vel = sc.rays_cone(s, seed=3, backoff=0.37 * ds)
+    p, v = torch.from_numpy(pos).pin_memory(), torch.from_numpy(vel).pin_memory()
+    pipe = HostStepPipeline(rif, h, ds, s * s, flags=DET, host_planes=(9, 7))
+    for _ in range(3):  # buffers recycled
+        k = pipe.submit(p, v)
+    g, st = pipe.result(k)
+    xt, vt = ops.trace(rif, p.cuda(), v.cuda(), h, ds, flags=DET)
+    one = torch.ones_like(xt)
+    ref = ops.backtrace(rif, xt, vt, one, one, h, ds, flags=DET)
+    assert g.shape == (7, ng, ng) and torch.equal(g, ref[9:16].cpu())
+    assert pipe.d2h_bytes == 7 * ng * ng * 4 + 16
+    with pytest.raises(RuntimeError):
+        HostStepPipeline(rif, h, ds, s * s, host_planes=(30, 7))
+
+
 @pytest.mark.parametrize("flags", [DET, 0])
 def test_graphed_step_replays_what_direct_calls_compute(flags, cuda_lib):
     """One captured CUDA graph, replayed over new ray batches and an in-place-updated grid."""
