@@ -534,7 +534,9 @@ def run_ours(args):
 
     # ---- this rank's batch ---------------------------------------------------------
     if strong and world > 1:  # sensor rows dealt out cyclically: every rank gets the same mix of cheap and expensive rays
-        sel = np.concatenate([np.arange(a, b) for a, b in shard_cyclic(n_total, rank, world, SENSOR)])
+        # blocks of one cell's worth of sensor rows (8 rows at 2048^2 / 256^3): neighbouring rows of a rank still share
+        # cells (L1 hits in the forward gather); profiles/r12_shard_block_ab.log
+        sel = np.concatenate([np.arange(a, b) for a, b in shard_cyclic(n_total, rank, world, SENSOR * max(1, SENSOR // NG))])
     else:
         sel = slice(0, n_total)
     pos_pin = torch.from_numpy(np.ascontiguousarray(pos_h[sel])).pin_memory()
@@ -733,7 +735,7 @@ def run_ours(args):
             "config": {
                 "workload": workload_name(),
                 "rays_total": n_total * (1 if strong else world), "rays_per_gpu": n_rays, "grid": [NG, NG, NG],
-                "parallelism": (f"rays-dp{world} (sensor rows of the one batch dealt out cyclically, dist.shard_cyclic) + private gradient grids + one gradient sum: {collective['used']}"
+                "parallelism": (f"rays-dp{world} (blocks of 8 sensor rows of the one batch dealt out cyclically, dist.shard_cyclic) + private gradient grids + one gradient sum: {collective['used']}"
                                 if world > 1 else "single GPU"),
                 "l2": (f"no explicit flush: per-step working set (rays in/out {n_rays * 72 / 1e6:.0f} MB + grid {NG ** 3 * 4 / 1e6:.0f} MB + "
                        f"gradient {NG ** 3 * 4 / 1e6:.0f} MB) exceeds the 126 MB L2"
