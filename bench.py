@@ -419,9 +419,22 @@ def run_ours(args):
     allreduce = GradAllReduce() if world > 1 else None
     collective = {"used": "ncclAllReduce (drrt_allreduce_grad)"} if world > 1 else None
 
-    host = workload_host()
-    rif_h, h, ds, pos_h, vel_h = host
-    rif = torch.from_numpy(rif_h).to(dev)
+    if NG >= 512:
+        # 512^3: the field is evaluated on the device (the float64 numpy meshgrid takes ~6 GB of host memory per
+        # process, x N ranks); same formula as scenes.field_bump, float64 then rounded to float32
+        from adjointnonlinearraytracing_b200 import scenes as sc
+        c = torch.arange(NG, device=dev, dtype=torch.float64) / (NG - 1)
+        r2 = (c - 0.5) ** 2
+        rif = (1.0 + 0.2 * torch.exp(-(r2[:, None, None] + r2[None, :, None] + r2[None, None, :]) / (2 * 0.2 * 0.2))
+               ).to(torch.float32).contiguous()
+        del c, r2
+        h = float(sc.grid_spacing(NG)); ds = h / 2
+        pos_h, vel_h = sc.rays_collimated(SENSOR)
+        host = None  # the cpu_baseline leg (N = 1 only) builds its own host copy
+    else:
+        host = workload_host()
+        rif_h, h, ds, pos_h, vel_h = host
+        rif = torch.from_numpy(rif_h).to(dev)
     n_total = pos_h.shape[0]
     strong = args.scaling == "strong"
     flags = 0
