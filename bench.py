@@ -698,8 +698,16 @@ def run_ours(args):
         counts = load("kernel_counts.json")  # tools/ncu_counts.py: per-launch ncu counters of THIS workload + csrc_sha
         l2p = load("l2_peaks.json")
         roof = None
-        if counts is not None and world == 1 and NG == 256:
-            k = counts["backtrace_kernel"]; kf = counts["trace_kernel"]
+        scaled = world > 1 or not strong  # this rank's launches cover a share of the batch the counts were taken on
+        if counts is not None and NG == 256 and (world == 1 or "warp_inst_per_warp_step" in counts["backtrace_kernel"]):
+            k = dict(counts["backtrace_kernel"]); kf = dict(counts["trace_kernel"])
+            if "warp_inst_per_warp_step" in k:  # same kernel, same batch geometry: instructions scale with the ray-steps
+                k["warp_inst"] = k["warp_inst_per_warp_step"] * s_b / 32.0
+                kf["warp_inst"] = kf["warp_inst_per_warp_step"] * s_f / 32.0
+                if world > 1:
+                    for d in (k, kf):
+                        for key in ("dram_bytes", "l1_red_sectors", "lts_sectors"):
+                            d[key] = None  # per-launch memory counters of the full batch do not carry over
             sm_mhz = (m["clocks"] or {}).get("sm_mhz") or counts.get("sm_mhz") or 1965
             pk_inst = 148 * 4 * sm_mhz * 1e6 / 1e9  # 4 schedulers x 1 warp instruction per clock per SM
             ai = k["warp_inst"] / (adj_ms * 1e-3) / 1e9
@@ -721,6 +729,7 @@ def run_ours(args):
                                "traffic": kf.get("dram_bytes")},
                 "counts_source": counts.get("source"), "counts_csrc_sha": counts.get("csrc_sha"), "built_csrc_sha": sha,
                 "stale": bool(counts.get("csrc_sha") != sha),
+                "counts_scaled_by_ray_steps": bool(scaled),  # N > 1: instructions per warp-step of the captured launch x this rank's ray-steps
             }
             if l2p is not None and k.get("l1_red_sectors"):
                 red = k["l1_red_sectors"] / (adj_ms * 1e-3) / 1e9

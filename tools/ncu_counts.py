@@ -3,7 +3,7 @@
 counters bench.py divides by LIVE kernel times for its roofline (read here, no GPU needed).  The file carries the
 hash of the kernel sources it was captured on; bench.py emits `stale: true` when the built sources differ.
 
-    python tools/ncu_counts.py gpurun_out/prof_adj_r12.ncu-rep gpurun_out/prof_fwd_r12.ncu-rep r12 > profiles/kernel_counts.json
+    python tools/ncu_counts.py gpurun_out/prof_adj_r12.ncu-rep gpurun_out/prof_fwd_r12.ncu-rep r12 [gpurun_out/bench_r12.json] > profiles/kernel_counts.json
 """
 import csv
 import io
@@ -63,6 +63,13 @@ def main():
            "source": f"profiles/{tag}_adj_full.txt, profiles/{tag}_fwd_full.txt (ncu --set full --clock-control none of `python bench.py "
                      "--steps 2 --warmup 3 --no-cpu --no-configs`, one launch each; tools/ncu_counts.py)",
            "backtrace_kernel": kernel(adj), "trace_kernel": kernel(fwd)}
+    if len(sys.argv) > 4:  # the bench line of the same build: ray-steps per launch -> instructions per warp-step
+        line = json.loads(open(sys.argv[4]).read().strip().splitlines()[-1])
+        cfg = line["config"]
+        sf = cfg.get("ray_steps_fwd_rank0", cfg.get("ray_steps_fwd")); sb = cfg.get("ray_steps_adj_rank0", cfg.get("ray_steps_adj"))
+        out["trace_kernel"]["ray_steps"] = sf; out["backtrace_kernel"]["ray_steps"] = sb
+        out["trace_kernel"]["warp_inst_per_warp_step"] = out["trace_kernel"]["warp_inst"] / (sf / 32.0)
+        out["backtrace_kernel"]["warp_inst_per_warp_step"] = out["backtrace_kernel"]["warp_inst"] / (sb / 32.0)
     print(json.dumps(out, indent=1))
 
 
