@@ -376,6 +376,31 @@ def config_lines(ops, torch, dev):
                 entry["graphed_step_error"] = repr(e)[:200]
         out.append(entry)
         del rif, pos, vel, xt, vt, one
+    # configs[0] the way the reference's driver batches it: SIX cube-face views per iteration, generated on the device with
+    # the random rigid rotation fused in (core/luneburg_opt.py:53-59 -> source.rand_rays_cube), through the 32^3 lens field
+    try:
+        from adjointnonlinearraytracing_b200 import source
+        from adjointnonlinearraytracing_b200.pipeline import GraphedStep
+        ng = 32
+        rif = T(sc.field_luneburg(ng)); h = float(sc.grid_spacing(ng)); ds = h / 2
+        rot = np.array([[0.36, 0.48, -0.8], [-0.8, 0.6, 0.0], [0.48, 0.64, 0.6]])  # a fixed rotation matrix
+        (pos, vel, _planes), _nr = source.rand_rays_cube((256, 256), 1, 1.0, circle=True, rotmat=rot, seed=0)
+        one = torch.ones_like(pos); g = torch.empty_like(rif); st = ops.new_stats(dev)
+        xt, vt = ops.trace(rif, pos, vel, h, ds, stats=st); sf = int(st[0]); st.zero_()
+        ops.backtrace(rif, xt, vt, one, one, h, ds, stats=st, out=g); sb = int(st[0])
+        tf = timed(lambda: ops.trace(rif, pos, vel, h, ds), 20)
+        tb = timed(lambda: ops.backtrace(rif, xt, vt, one, one, h, ds, out=g), 20)
+        gs = GraphedStep(rif, h, ds, int(pos.shape[0])); gs.step(pos, vel)
+        tg = timed(lambda: gs.step(), 20)
+        out.insert(1, {"name": "luneburg32_cube6", "label": "configs[0] as the reference's driver batches it: six cube-face views per iteration "
+                       "(256^2 pixels each, circle filter, random rotation; generated on the device) through the 32^3 lens field",
+                       "grid": [ng, ng, ng], "rays": int(pos.shape[0]), "fwd_ms": tf, "adj_ms": tb,
+                       "fwd_ray_steps_per_s": sf / (tf * 1e-3), "adj_ray_steps_per_s": sb / (tb * 1e-3),
+                       "ray_steps_per_s": (sf + sb) / ((tf + tb) * 1e-3), "graphed_step_ms": tg,
+                       "graphed_ray_steps_per_s": (sf + sb) / (tg * 1e-3)})
+        del gs, rif, pos, vel, xt, vt, one, g
+    except Exception as e:
+        out.insert(1, {"name": "luneburg32_cube6", "error": repr(e)[:200]})
     # the reference's protocol: 33^3, 512^2 collimated rays from z = 0, step sizes 0.3 .. 1.2 h, all-ones seeds
     ng = 33
     rif = T(sc.field_bump(ng)); h = float(sc.grid_spacing(ng))
