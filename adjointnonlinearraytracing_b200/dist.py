@@ -131,6 +131,8 @@ class SwitchAllReduce:
             n *= int(d)
         if n % 4:
             raise RuntimeError("SwitchAllReduce: the grid must hold a multiple of 4 floats")
+        if self.world == 1:  # nothing to sum: any buffer will do
+            return torch.empty(tuple(int(d) for d in shape), dtype=torch.float32, device=device)
         with torch.cuda.device(device):
             buf = self._symm.empty(n, dtype=torch.float32, device=torch.device(device))
             hdl = self._symm.rendezvous(buf, self.group.group_name)
@@ -147,7 +149,9 @@ class SwitchAllReduce:
         ent = self._handles.get(grad.data_ptr())
         if ent is None:
             raise RuntimeError("SwitchAllReduce: grad must be a buffer returned by alloc()")
-        hdl, mc, _ = ent
+        hdl, mc, buf = ent
+        if grad.numel() != buf.numel() or not grad.is_contiguous():
+            raise RuntimeError("SwitchAllReduce: grad must be the whole contiguous buffer returned by alloc()")
         with torch.cuda.device(grad.device):
             stream = c_void_p(torch.cuda.current_stream(grad.device).cuda_stream)
             hdl.barrier(channel=0)  # every rank's adjoint has finished writing its copy
